@@ -1,0 +1,143 @@
+/* libpyhgf_cuda -- C ABI of the B200 (sm_100a) belief-propagation backend.
+ *
+ * The reference (ComputationalPsychiatry/pyhgf) has no FFI on this path: the
+ * JAX implementation is traced Python (pyhgf/model/network.py:528-628 runs
+ * `lax.scan(beliefs_propagation, ...)`), the Rust one is a PyO3 class
+ * (src/model/network.rs:1415-1434).  These entry points are what a binding for
+ * the path would call; INTEGRATION.md shows the ctypes and XLA-FFI stubs.
+ *
+ * Conventions: return 0 on success, non-zero on invalid arguments or a CUDA
+ * error (text via hgf_last_error(), thread-local).  Numerical failure is NOT
+ * an error: NaN / +inf flow in-band exactly as in the reference
+ * (prediction/continuous.py:229-231, response.py:48).  The caller owns every
+ * buffer.  Device entry points enqueue on `stream` and never synchronise; the
+ * *_host entry points take host pointers, stage through the device and return
+ * after the results are back in the caller's buffers.
+ */
+#ifndef PYHGF_CUDA_H_
+#define PYHGF_CUDA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HGF_ABI_VERSION 1
+
+/* number of scalar attribute fields per node, and their order (slot = node * HGF_N_FIELDS + field).
+ * Names are the reference's attribute keys, pyhgf/model/add_nodes.py:65-85, 159-184, 330-340. */
+#define HGF_N_FIELDS 19
+#define HGF_N_RESPONSE_PARAMETERS 4
+
+typedef struct hgf_plan hgf_plan_t;
+
+/* What pyhgf.Network.get_network() returns, flattened (pyhgf/model/network.py:769-776):
+ * edges (pyhgf/typing/typing.py:12-52, CSR), the update sequence
+ * (pyhgf/utils/get_update_sequence.py:51-351, opcodes below) and the constructor
+ * constants (pyhgf/model/network.py:85-91). */
+typedef struct {
+  int32_t n_nodes;
+  const int32_t* node_type;               /* [n_nodes] 1 binary, 2 continuous, 6 volatile */
+  const int32_t* value_parents_ptr;       /* [n_nodes+1] */
+  const int32_t* value_parents_idx;
+  const int32_t* volatility_parents_ptr;  /* [n_nodes+1] */
+  const int32_t* volatility_parents_idx;
+  const int32_t* value_children_ptr;      /* [n_nodes+1] */
+  const int32_t* value_children_idx;
+  const int32_t* value_children_fn;       /* coupling function per value child: hgf_coupling_fn */
+  const int32_t* volatility_children_ptr; /* [n_nodes+1] */
+  const int32_t* volatility_children_idx;
+  int32_t n_prediction_steps;
+  const int32_t* prediction_node;
+  const int32_t* prediction_op;           /* hgf_op */
+  int32_t n_update_steps;
+  const int32_t* update_node;
+  const int32_t* update_op;
+  int32_t n_inputs;                       /* Network.input_idxs, network.py:157-180 */
+  const int32_t* input_idxs;
+  int32_t n_fed;                          /* leading input nodes that receive a data column */
+  int32_t volatility_updates;             /* 0 unbounded, 1 eHGF, 2 standard */
+  int32_t mean_field_updates;
+  double max_posterior_precision;
+} hgf_topology_t;
+
+enum hgf_coupling_fn { HGF_CF_LINEAR = 0, HGF_CF_IDENTITY = 1, HGF_CF_RELU = 2, HGF_CF_SIGMOID = 3, HGF_CF_TANH = 4,
+                       HGF_CF_LEAKY_RELU = 5, HGF_CF_GELU = 6, HGF_CF_SIN = 7 };
+
+enum hgf_op { HGF_OP_PRED_BINARY = 1, HGF_OP_PRED_CONT = 2, HGF_OP_PRED_CONT_MF = 3, HGF_OP_PRED_VOLATILE = 4,
+              HGF_OP_PRED_VOLATILE_MF = 5, HGF_OP_PE_BINARY = 10, HGF_OP_PE_CONT = 11, HGF_OP_PE_VOLATILE = 12,
+              HGF_OP_POST_CONT = 20, HGF_OP_POST_CONT_MF = 21, HGF_OP_POST_CONT_EHGF = 22, HGF_OP_POST_CONT_EHGF_MF = 23,
+              HGF_OP_POST_CONT_UNBOUNDED = 24, HGF_OP_POST_VOLATILE = 25, HGF_OP_POST_VOLATILE_MF = 26 };
+
+/* the built-in response functions of pyhgf/response.py:15-215 */
+enum hgf_response { HGF_RESP_NONE = 0, HGF_RESP_FIRST_LEVEL_GAUSSIAN = 1, HGF_RESP_TOTAL_GAUSSIAN = 2,
+                    HGF_RESP_FIRST_LEVEL_BINARY = 3, HGF_RESP_BINARY_SOFTMAX = 4,
+                    HGF_RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE = 5 };
+
+/* One batched evaluation: N independent instances of the plan's network, T time steps.
+ * Replaces Network.input_data (+ Network.surprise / the vmap'd logp pattern) for the batch.
+ * All arrays are dense; element type is float (dtype 32) or double (dtype 64). */
+typedef struct {
+  int32_t dtype;                 /* 32 or 64 */
+  int64_t n_instances;           /* N */
+  int32_t n_steps;               /* T */
+  /* observations: instance n reads series n / input_group_size (0: one series shared by all) */
+  int64_t input_group_size;
+  const void* input_data;        /* [G][T][n_fed] */
+  const uint8_t* observed;       /* [G][T][n_fed] or NULL (all observed) */
+  const void* time_steps;        /* [T] or NULL (all 1) */
+  /* attributes: the initial attribute vector shared by all instances, with per-instance overrides */
+  const void* attributes;        /* [n_slots], see hgf_plan_n_slots / hgf_plan_slot_* */
+  int32_t n_params;              /* P <= 16 */
+  const int32_t* param_slots;    /* HOST [P]: slot each per-instance parameter overrides */
+  const void* params;            /* [P][N] */
+  /* response (surprise) function fused into the time loop */
+  int32_t response_fn;           /* hgf_response */
+  int64_t response_group_size;   /* grouping of response_inputs, like input_group_size */
+  const void* response_inputs;   /* [G][T] or NULL */
+  /* outputs (each may be NULL) */
+  int32_t n_records;
+  const int32_t* record_slots;   /* HOST [R]: attribute slots recorded at every step */
+  void* trajectories;            /* [R][T][N] (time-major: stores coalesce over instances) */
+  void* last_attributes;         /* [n_nodes*HGF_N_FIELDS][N] */
+  void* surprise_sum;            /* [N]  out_scale * sum_t surprise  (out_scale = -1: log-probability) */
+  void* surprise_pointwise;      /* [T][N] (unscaled) */
+  void* gradient;                /* [P][N] d(surprise_sum)/d(params); hgf_logp_grad only */
+  void* reduced;                 /* [n_groups] += surprise_sum of the instances of each group; caller zeroes it */
+  const int32_t* group;          /* [N] group (e.g. chain) of each instance, or NULL: everything into reduced[0] */
+  double out_scale;
+} hgf_call_t;
+
+int hgf_abi_version(void);
+const char* hgf_last_error(void);
+
+int hgf_plan_create(const hgf_topology_t* topology, hgf_plan_t** out);
+void hgf_plan_destroy(hgf_plan_t* plan);
+
+/* attribute-vector layout */
+int32_t hgf_plan_n_slots(const hgf_plan_t* plan);
+/* kind: 0 value_coupling_parents, 1 volatility_coupling_parents, 2 value_coupling_children,
+ * 3 volatility_coupling_children */
+int32_t hgf_plan_slot_coupling(const hgf_plan_t* plan, int32_t kind, int32_t node, int32_t position);
+int32_t hgf_plan_slot_clipping(const hgf_plan_t* plan);   /* attributes[-1]["precision_clipping_value"] */
+int32_t hgf_plan_slot_response(const hgf_plan_t* plan);   /* first response-function parameter */
+/* name of the kernel variant the plan dispatches to ("interpreter" or a register-resident specialisation) */
+const char* hgf_plan_kernel_name(const hgf_plan_t* plan);
+
+/* Forward filter (+ fused surprise).  Device pointers; enqueued on `stream` (a cudaStream_t). */
+int hgf_filter(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
+/* Forward filter + d(surprise_sum)/d(params) in the same pass.  Device pointers. */
+int hgf_logp_grad(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
+
+/* Same, with every data pointer in HOST memory (pageable or pinned); copies in, runs, copies out, synchronises. */
+int hgf_filter_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device);
+int hgf_logp_grad_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device);
+
+/* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
+int64_t hgf_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* PYHGF_CUDA_H_ */

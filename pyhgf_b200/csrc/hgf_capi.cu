@@ -1,0 +1,329 @@
+// C ABI of libpyhgf_cuda (include/pyhgf_cuda.h): plan creation (lowering the
+// flattened pyhgf network description into the kernels' Program), dispatch to
+// the kernel variant, and the host-buffer convenience entry points.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/pyhgf_cuda.h"
+#include "hgf_dispatch.h"
+
+using namespace hgf;
+
+static_assert(NF == HGF_N_FIELDS, "field count out of sync with the public header");
+static_assert(N_RESP_PARAMS == HGF_N_RESPONSE_PARAMETERS, "response parameter count out of sync");
+
+static thread_local std::string g_error;
+static std::atomic<long long> g_launches{0};
+
+static int fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_error = buf;
+  return 1;
+}
+
+struct hgf_plan {
+  Program prog;
+  const KernelVariant* variant;
+};
+
+extern "C" {
+
+int hgf_abi_version(void) { return HGF_ABI_VERSION; }
+const char* hgf_last_error(void) { return g_error.c_str(); }
+int64_t hgf_launch_count(void) { return g_launches.load(); }
+
+int hgf_plan_create(const hgf_topology_t* t, hgf_plan_t** out) {
+  if (!t || !out) return fail("hgf_plan_create: null argument");
+  *out = nullptr;
+  const int n = t->n_nodes;
+  if (n < 1 || n > MAX_NODES) return fail("hgf_plan_create: n_nodes=%d outside [1, %d]", n, MAX_NODES);
+  if (t->n_prediction_steps < 0 || t->n_prediction_steps > MAX_STEPS || t->n_update_steps < 0 || t->n_update_steps > MAX_STEPS)
+    return fail("hgf_plan_create: schedule longer than %d steps", MAX_STEPS);
+  if (t->n_inputs < 0 || t->n_inputs > MAX_INPUTS || t->n_fed < 0 || t->n_fed > t->n_inputs)
+    return fail("hgf_plan_create: n_inputs=%d / n_fed=%d invalid (max %d)", t->n_inputs, t->n_fed, MAX_INPUTS);
+  if (t->volatility_updates < 0 || t->volatility_updates > 2) return fail("hgf_plan_create: volatility_updates must be 0, 1 or 2");
+  hgf_plan* plan = new (std::nothrow) hgf_plan();
+  if (!plan) return fail("hgf_plan_create: out of memory");
+  Program& p = plan->prog;
+  std::memset(&p, 0, sizeof p);
+  p.n_nodes = n;
+  p.n_pred = t->n_prediction_steps;
+  p.n_upd = t->n_update_steps;
+  p.n_inputs = t->n_inputs;
+  p.n_fed = t->n_fed;
+  p.vol_updates = t->volatility_updates;
+  p.mean_field = t->mean_field_updates ? 1 : 0;
+  p.max_posterior_precision = t->max_posterior_precision;
+
+  auto fill = [&](const int32_t* ptr, const int32_t* idx, uint8_t* count, uint8_t* off, uint8_t* dst, const char* what) -> int {
+    if (!ptr) return fail("hgf_plan_create: %s_ptr is null", what);
+    if (ptr[n] > MAX_EDGES) return fail("hgf_plan_create: more than %d %s edges", MAX_EDGES, what);
+    for (int i = 0; i < n; ++i) {
+      const int c = ptr[i + 1] - ptr[i];
+      if (c < 0 || c > 255) return fail("hgf_plan_create: bad %s CSR", what);
+      count[i] = static_cast<uint8_t>(c);
+      off[i] = static_cast<uint8_t>(ptr[i]);
+      for (int k = ptr[i]; k < ptr[i + 1]; ++k) {
+        if (idx[k] < 0 || idx[k] >= n) return fail("hgf_plan_create: %s index %d out of range", what, idx[k]);
+        dst[k] = static_cast<uint8_t>(idx[k]);
+      }
+    }
+    return 0;
+  };
+  int rc = 0;
+  rc = rc || fill(t->value_parents_ptr, t->value_parents_idx, p.n_vp, p.off_vp, p.e_vp, "value_parents");
+  rc = rc || fill(t->volatility_parents_ptr, t->volatility_parents_idx, p.n_volp, p.off_volp, p.e_volp, "volatility_parents");
+  rc = rc || fill(t->value_children_ptr, t->value_children_idx, p.n_vc, p.off_vc, p.e_vc, "value_children");
+  rc = rc || fill(t->volatility_children_ptr, t->volatility_children_idx, p.n_volc, p.off_volc, p.e_volc, "volatility_children");
+  if (rc) { delete plan; return 1; }
+
+  for (int i = 0; i < n; ++i) {
+    const int ty = t->node_type[i];
+    if (ty != NODE_BINARY && ty != NODE_CONTINUOUS && ty != NODE_VOLATILE) {
+      delete plan;
+      return fail("hgf_plan_create: node %d has type %d; this backend runs binary (1), continuous (2) and volatile (6) state nodes", i, ty);
+    }
+    p.node_type[i] = static_cast<uint8_t>(ty);
+    for (int k = 0; k < p.n_vc[i]; ++k) {
+      const int fn = t->value_children_fn ? t->value_children_fn[t->value_children_ptr[i] + k] : 0;
+      if (fn < 0 || fn > CF_SIN) { delete plan; return fail("hgf_plan_create: unknown coupling function %d", fn); }
+      p.e_vc_fn[p.off_vc[i] + k] = static_cast<uint8_t>(fn);
+    }
+  }
+  // coupling function as seen from the child: the parent's entry for this child
+  for (int i = 0; i < n; ++i)
+    for (int k = 0; k < p.n_vp[i]; ++k) {
+      const int par = p.e_vp[p.off_vp[i] + k];
+      int fn = -1;
+      for (int j = 0; j < p.n_vc[par]; ++j)
+        if (p.e_vc[p.off_vc[par] + j] == i) { fn = p.e_vc_fn[p.off_vc[par] + j]; break; }
+      if (fn < 0) { delete plan; return fail("hgf_plan_create: node %d lists value parent %d, which does not list it as a child", i, par); }
+      p.e_vp_fn[p.off_vp[i] + k] = static_cast<uint8_t>(fn);
+    }
+  auto valid_op = [](int op) {
+    return (op >= OP_PRED_BINARY && op <= OP_PRED_VOLATILE_MF) || (op >= OP_PE_BINARY && op <= OP_PE_VOLATILE) ||
+           (op >= OP_POST_CONT && op <= OP_POST_VOLATILE_MF);
+  };
+  for (int i = 0; i < p.n_pred; ++i) {
+    if (!valid_op(t->prediction_op[i]) || t->prediction_node[i] < 0 || t->prediction_node[i] >= n) { delete plan; return fail("hgf_plan_create: bad prediction step %d", i); }
+    p.pred_node[i] = static_cast<uint8_t>(t->prediction_node[i]);
+    p.pred_op[i] = static_cast<uint8_t>(t->prediction_op[i]);
+  }
+  for (int i = 0; i < p.n_upd; ++i) {
+    if (!valid_op(t->update_op[i]) || t->update_node[i] < 0 || t->update_node[i] >= n) { delete plan; return fail("hgf_plan_create: bad update step %d", i); }
+    if (t->update_op[i] == OP_POST_CONT_UNBOUNDED && p.n_volc[t->update_node[i]] == 0) { delete plan; return fail("hgf_plan_create: unbounded update on node %d without volatility children", t->update_node[i]); }
+    p.upd_node[i] = static_cast<uint8_t>(t->update_node[i]);
+    p.upd_op[i] = static_cast<uint8_t>(t->update_op[i]);
+  }
+  for (int k = 0; k < p.n_inputs; ++k) {
+    if (t->input_idxs[k] < 0 || t->input_idxs[k] >= n) { delete plan; return fail("hgf_plan_create: input index out of range"); }
+    p.input_idx[k] = static_cast<uint8_t>(t->input_idxs[k]);
+  }
+  int off = n * NF;
+  p.base_cvp = off; off += t->value_parents_ptr[n];
+  p.base_cvolp = off; off += t->volatility_parents_ptr[n];
+  p.base_cvc = off; off += t->value_children_ptr[n];
+  p.base_cvolc = off; off += t->volatility_children_ptr[n];
+  p.slot_clip = off++;
+  p.slot_resp = off; off += N_RESP_PARAMS;
+  p.n_slots = off;
+  plan->variant = select_variant(p);
+  if (!plan->variant->match && p.n_slots > INTERP_SLOTS) {
+    delete plan;
+    return fail("hgf_plan_create: network needs %d attribute slots; the interpreter holds %d", off, INTERP_SLOTS);
+  }
+  *out = plan;
+  return 0;
+}
+
+void hgf_plan_destroy(hgf_plan_t* plan) { delete plan; }
+
+int32_t hgf_plan_n_slots(const hgf_plan_t* plan) { return plan ? plan->prog.n_slots : -1; }
+int32_t hgf_plan_slot_coupling(const hgf_plan_t* plan, int32_t kind, int32_t node, int32_t pos) {
+  if (!plan || node < 0 || node >= plan->prog.n_nodes || pos < 0) return -1;
+  const Program& p = plan->prog;
+  switch (kind) {
+    case 0: return pos < p.n_vp[node] ? p.base_cvp + p.off_vp[node] + pos : -1;
+    case 1: return pos < p.n_volp[node] ? p.base_cvolp + p.off_volp[node] + pos : -1;
+    case 2: return pos < p.n_vc[node] ? p.base_cvc + p.off_vc[node] + pos : -1;
+    case 3: return pos < p.n_volc[node] ? p.base_cvolc + p.off_volc[node] + pos : -1;
+  }
+  return -1;
+}
+int32_t hgf_plan_slot_clipping(const hgf_plan_t* plan) { return plan ? plan->prog.slot_clip : -1; }
+int32_t hgf_plan_slot_response(const hgf_plan_t* plan) { return plan ? plan->prog.slot_resp : -1; }
+const char* hgf_plan_kernel_name(const hgf_plan_t* plan) { return plan ? plan->variant->name : ""; }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// launch
+// ---------------------------------------------------------------------------
+static int check_call(const hgf_plan_t* plan, const hgf_call_t* c, bool want_grad, CallLists& lists) {
+  if (!plan || !c) return fail("null plan or call");
+  const Program& p = plan->prog;
+  if (c->dtype != 32 && c->dtype != 64) return fail("dtype must be 32 or 64, got %d", c->dtype);
+  if (c->n_instances < 0 || c->n_steps < 0) return fail("negative n_instances / n_steps");
+  if (!c->attributes) return fail("attributes is null");
+  if (p.n_fed > 0 && c->n_steps > 0 && !c->input_data) return fail("input_data is null");
+  if (c->n_params < 0 || c->n_params > MAX_PARAMS) return fail("n_params=%d outside [0, %d]", c->n_params, MAX_PARAMS);
+  if (c->n_params > 0 && (!c->param_slots || !c->params)) return fail("params / param_slots is null");
+  if (c->n_records < 0 || c->n_records > MAX_RECORDS) return fail("n_records=%d outside [0, %d]", c->n_records, MAX_RECORDS);
+  if (c->trajectories && c->n_records > 0 && !c->record_slots) return fail("record_slots is null");
+  if (c->response_fn < RESP_NONE || c->response_fn > RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE) return fail("unknown response_fn %d", c->response_fn);
+  if ((c->response_fn == RESP_BINARY_SOFTMAX || c->response_fn == RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE) && !c->response_inputs)
+    return fail("response function %d needs response_inputs", c->response_fn);
+  if ((c->response_fn == RESP_FIRST_LEVEL_GAUSSIAN) && p.n_nodes < 2) return fail("first_level_gaussian_surprise needs a node 1");
+  if (c->input_group_size < 0 || c->response_group_size < 0) return fail("negative group size");
+  if (want_grad && !c->gradient) return fail("hgf_logp_grad: gradient is null");
+  if (want_grad && c->n_params < 1) return fail("hgf_logp_grad: no per-instance parameter to differentiate");
+  if (!want_grad && c->gradient) return fail("hgf_filter: gradient must be null (use hgf_logp_grad)");
+  std::memset(&lists, 0, sizeof lists);
+  lists.n_params = c->n_params;
+  for (int i = 0; i < c->n_params; ++i) {
+    if (c->param_slots[i] < 0 || c->param_slots[i] >= p.n_slots) return fail("param slot %d out of range", c->param_slots[i]);
+    lists.param_slot[i] = static_cast<uint16_t>(c->param_slots[i]);
+  }
+  lists.n_rec = c->trajectories ? c->n_records : 0;
+  for (int i = 0; i < lists.n_rec; ++i) {
+    if (c->record_slots[i] < 0 || c->record_slots[i] >= p.n_slots) return fail("record slot %d out of range", c->record_slots[i]);
+    lists.rec_slot[i] = static_cast<uint16_t>(c->record_slots[i]);
+  }
+  return 0;
+}
+
+static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stream, bool want_grad) {
+  CallLists lists;
+  if (check_call(plan, c, want_grad, lists)) return 1;
+  if (c->n_instances == 0) return 0;
+  ScanArgs a;
+  std::memset(&a, 0, sizeof a);
+  a.n_instances = c->n_instances;
+  a.n_steps = c->n_steps;
+  a.input_group_size = c->input_group_size;
+  a.response_group_size = c->response_group_size;
+  a.input_data = c->input_data;
+  a.observed = c->observed;
+  a.time_steps = c->time_steps;
+  a.attributes = c->attributes;
+  a.params = c->params;
+  a.response_inputs = c->response_inputs;
+  a.trajectories = c->trajectories;
+  a.last_attributes = c->last_attributes;
+  a.surprise_sum = c->surprise_sum;
+  a.surprise_pointwise = c->surprise_pointwise;
+  a.gradient = want_grad ? c->gradient : nullptr;
+  a.reduced = c->reduced;
+  a.group = c->group;
+  a.out_scale = c->out_scale;
+  a.response_fn = c->response_fn;
+  int n_launched = 0;
+  cudaError_t err = run_variant(*plan->variant, plan->prog, lists, a, c->dtype, want_grad, stream, &n_launched);
+  g_launches += n_launched;
+  if (err != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(err));
+  return 0;
+}
+
+extern "C" int hgf_filter(const hgf_plan_t* plan, const hgf_call_t* call, void* stream) {
+  return launch(plan, call, static_cast<cudaStream_t>(stream), false);
+}
+extern "C" int hgf_logp_grad(const hgf_plan_t* plan, const hgf_call_t* call, void* stream) {
+  return launch(plan, call, static_cast<cudaStream_t>(stream), true);
+}
+
+// ---------------------------------------------------------------------------
+// host-buffer entry points: stage in, run, stage out
+// ---------------------------------------------------------------------------
+namespace {
+struct Staging {
+  cudaStream_t stream = nullptr;
+  std::vector<void*> device;
+  struct Out { void* dev; void* host; size_t bytes; };
+  std::vector<Out> outs;
+  cudaError_t err = cudaSuccess;
+  const void* in(const void* host, size_t bytes) {
+    if (!host || bytes == 0 || err != cudaSuccess) return nullptr;
+    void* d = nullptr;
+    err = cudaMallocAsync(&d, bytes, stream);
+    if (err != cudaSuccess) return nullptr;
+    device.push_back(d);
+    err = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, stream);
+    return d;
+  }
+  void* out(void* host, size_t bytes, bool zero_from_host = false) {
+    if (!host || bytes == 0 || err != cudaSuccess) return nullptr;
+    void* d = nullptr;
+    err = cudaMallocAsync(&d, bytes, stream);
+    if (err != cudaSuccess) return nullptr;
+    device.push_back(d);
+    if (zero_from_host) err = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, stream);
+    outs.push_back({d, host, bytes});
+    return d;
+  }
+  void finish() {
+    if (err == cudaSuccess)
+      for (auto& o : outs) {
+        err = cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, stream);
+        if (err != cudaSuccess) break;
+      }
+    for (void* d : device) cudaFreeAsync(d, stream);
+    cudaError_t e2 = cudaStreamSynchronize(stream);
+    if (err == cudaSuccess) err = e2;
+  }
+};
+}  // namespace
+
+static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, bool want_grad) {
+  CallLists lists;
+  if (check_call(plan, c, want_grad, lists)) return 1;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return fail("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  const Program& p = plan->prog;
+  const size_t w = c->dtype == 32 ? 4 : 8;
+  const size_t N = static_cast<size_t>(c->n_instances), T = static_cast<size_t>(c->n_steps);
+  const size_t n_in_series = c->input_group_size > 0 ? (N + c->input_group_size - 1) / c->input_group_size : 1;
+  const size_t n_resp_series = c->response_group_size > 0 ? (N + c->response_group_size - 1) / c->response_group_size : 1;
+  int n_groups = 1;
+  if (c->reduced && c->group)
+    for (size_t i = 0; i < N; ++i) n_groups = c->group[i] + 1 > n_groups ? c->group[i] + 1 : n_groups;
+  Staging st;
+  e = cudaStreamCreateWithFlags(&st.stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) return fail("cudaStreamCreate: %s", cudaGetErrorString(e));
+  hgf_call_t d = *c;
+  d.input_data = st.in(c->input_data, n_in_series * T * p.n_fed * w);
+  d.observed = static_cast<const uint8_t*>(st.in(c->observed, n_in_series * T * p.n_fed));
+  d.time_steps = st.in(c->time_steps, T * w);
+  d.attributes = st.in(c->attributes, static_cast<size_t>(p.n_slots) * w);
+  d.params = st.in(c->params, static_cast<size_t>(c->n_params) * N * w);
+  d.response_inputs = st.in(c->response_inputs, n_resp_series * T * w);
+  d.group = static_cast<const int32_t*>(st.in(c->group, N * sizeof(int32_t)));
+  d.trajectories = st.out(c->trajectories, static_cast<size_t>(lists.n_rec) * T * N * w);
+  d.last_attributes = st.out(c->last_attributes, static_cast<size_t>(p.n_nodes) * NF * N * w);
+  d.surprise_sum = st.out(c->surprise_sum, N * w);
+  d.surprise_pointwise = st.out(c->surprise_pointwise, T * N * w);
+  d.gradient = want_grad ? st.out(c->gradient, static_cast<size_t>(c->n_params) * N * w) : nullptr;
+  d.reduced = st.out(c->reduced, static_cast<size_t>(n_groups) * w, true);
+  int rc = 0;
+  if (st.err == cudaSuccess) rc = launch(plan, &d, st.stream, want_grad);
+  st.finish();
+  cudaStreamDestroy(st.stream);
+  if (rc) return rc;
+  if (st.err != cudaSuccess) return fail("host staging failed: %s", cudaGetErrorString(st.err));
+  return 0;
+}
+
+extern "C" int hgf_filter_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device) {
+  return run_host(plan, call, device, false);
+}
+extern "C" int hgf_logp_grad_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device) {
+  return run_host(plan, call, device, true);
+}

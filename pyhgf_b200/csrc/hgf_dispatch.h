@@ -1,0 +1,31 @@
+// Kernel variants: the opcode interpreter (any topology) and the generated
+// register-resident specialisations (matched by exact Program equality).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "hgf_program.h"
+
+namespace hgf {
+
+using RunFn = cudaError_t (*)(const Program&, const CallLists&, const ScanArgs&, int dtype, bool want_grad, cudaStream_t,
+                              int* n_launched);
+
+struct KernelVariant {
+  const char* name;
+  const Program* match;  // nullptr: accepts every program
+  RunFn run;
+};
+
+// hgf_interp.cu
+extern const KernelVariant kInterpreterVariant;
+// hgf_static.cu (generated tables): null-terminated list
+const KernelVariant* const* static_variants();
+
+const KernelVariant* select_variant(const Program& prog);
+
+inline cudaError_t run_variant(const KernelVariant& v, const Program& prog, const CallLists& lists, const ScanArgs& args, int dtype,
+                               bool want_grad, cudaStream_t stream, int* n_launched) {
+  return v.run(prog, lists, args, dtype, want_grad, stream, n_launched);
+}
+
+}  // namespace hgf

@@ -1,0 +1,110 @@
+// The lowered form of one network: what the host-side topology compiler
+// (pyhgf_b200/topology.py, following pyhgf/utils/get_update_sequence.py:51-351)
+// hands to the kernels.  Plain data, passed to the kernel by value as a
+// __grid_constant__ parameter (uniform constant-bank reads).
+#pragma once
+#include <stdint.h>
+
+namespace hgf {
+
+constexpr int MAX_NODES = 32;
+constexpr int MAX_EDGES = 96;     // per edge kind
+constexpr int MAX_STEPS = 96;     // prediction steps / update steps
+constexpr int MAX_INPUTS = 16;
+constexpr int MAX_RECORDS = 640;  // recorded (node, field) leaves
+constexpr int MAX_PARAMS = 16;    // batched (per-instance) parameters
+constexpr int N_RESP_PARAMS = 4;
+constexpr int INTERP_SLOTS = 768;  // attribute-vector capacity of the opcode interpreter
+
+// node_type codes: pyhgf/typing/typing.py:12-52
+enum NodeType : int { NODE_CONSTANT = 0, NODE_BINARY = 1, NODE_CONTINUOUS = 2, NODE_VOLATILE = 6 };
+
+// coupling functions: `None` in the reference is LINEAR; the rest is the
+// enumerated set a C-ABI can carry (src/math.rs:41-55) plus sin/identity.
+enum CouplingFn : int { CF_LINEAR = 0, CF_IDENTITY = 1, CF_RELU = 2, CF_SIGMOID = 3, CF_TANH = 4, CF_LEAKY_RELU = 5, CF_GELU = 6, CF_SIN = 7 };
+
+enum Op : int {
+  OP_PRED_BINARY = 1, OP_PRED_CONT = 2, OP_PRED_CONT_MF = 3, OP_PRED_VOLATILE = 4, OP_PRED_VOLATILE_MF = 5,
+  OP_PE_BINARY = 10, OP_PE_CONT = 11, OP_PE_VOLATILE = 12,
+  OP_POST_CONT = 20, OP_POST_CONT_MF = 21, OP_POST_CONT_EHGF = 22, OP_POST_CONT_EHGF_MF = 23,
+  OP_POST_CONT_UNBOUNDED = 24, OP_POST_VOLATILE = 25, OP_POST_VOLATILE_MF = 26,
+};
+
+enum VolUpdates : int { VU_UNBOUNDED = 0, VU_EHGF = 1, VU_STANDARD = 2 };
+
+// pyhgf/response.py
+enum Response : int {
+  RESP_NONE = 0, RESP_FIRST_LEVEL_GAUSSIAN = 1, RESP_TOTAL_GAUSSIAN = 2, RESP_FIRST_LEVEL_BINARY = 3,
+  RESP_BINARY_SOFTMAX = 4, RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE = 5,
+};
+
+// Per-node scalar attributes.  slot = node * NF + field; the names are the
+// reference's attribute keys (pyhgf/model/add_nodes.py:65-85, 159-184, 330-340)
+// with `temp.*` flattened.
+enum Field : int {
+  F_MEAN = 0, F_EXPECTED_MEAN, F_PRECISION, F_EXPECTED_PRECISION,
+  F_TONIC_VOLATILITY, F_TONIC_DRIFT, F_AUTOCONNECTION_STRENGTH, F_OBSERVED,
+  F_MEAN_VOL, F_EXPECTED_MEAN_VOL, F_PRECISION_VOL, F_EXPECTED_PRECISION_VOL, F_TONIC_VOLATILITY_VOL,
+  F_EFFECTIVE_PRECISION, F_CONDITIONAL_EXPECTED_PRECISION, F_VALUE_PREDICTION_ERROR,
+  F_VOLATILITY_PREDICTION_ERROR, F_CURRENT_VARIANCE, F_EFFECTIVE_PRECISION_VOL,
+  NF
+};
+
+// Slot layout of one instance's attribute vector:
+//   [0, n_nodes*NF)                          node fields
+//   base_cvp   + off_vp[node]   + k          value_coupling_parents[k]
+//   base_cvolp + off_volp[node] + k          volatility_coupling_parents[k]
+//   base_cvc   + off_vc[node]   + k          value_coupling_children[k]
+//   base_cvolc + off_volc[node] + k          volatility_coupling_children[k]
+//   slot_clip                                precision_clipping_value
+//   slot_resp + j                            response-function parameter j
+struct Program {
+  int32_t n_nodes, n_slots;
+  int32_t n_pred, n_upd;
+  int32_t n_inputs, n_fed;
+  int32_t vol_updates, mean_field;
+  int32_t base_cvp, base_cvolp, base_cvc, base_cvolc, slot_clip, slot_resp;
+  double max_posterior_precision;
+  uint8_t node_type[MAX_NODES];
+  uint8_t n_vp[MAX_NODES], n_volp[MAX_NODES], n_vc[MAX_NODES], n_volc[MAX_NODES];
+  uint8_t off_vp[MAX_NODES], off_volp[MAX_NODES], off_vc[MAX_NODES], off_volc[MAX_NODES];
+  uint8_t e_vp[MAX_EDGES], e_vp_fn[MAX_EDGES];  // value parents and the coupling fn the parent applies to this child
+  uint8_t e_volp[MAX_EDGES];
+  uint8_t e_vc[MAX_EDGES], e_vc_fn[MAX_EDGES];
+  uint8_t e_volc[MAX_EDGES];
+  uint8_t pred_node[MAX_STEPS], pred_op[MAX_STEPS];
+  uint8_t upd_node[MAX_STEPS], upd_op[MAX_STEPS];
+  uint8_t input_idx[MAX_INPUTS];
+};
+
+// Per-call lists (which leaves are recorded, which slots are per-instance).
+struct CallLists {
+  int32_t n_rec, n_params;
+  uint16_t rec_slot[MAX_RECORDS];
+  uint16_t param_slot[MAX_PARAMS];
+};
+
+// One launch's arguments (device pointers; see hgf_call_t in include/pyhgf_cuda.h).
+struct ScanArgs {
+  long long n_instances;
+  int n_steps;
+  long long input_group_size, response_group_size;
+  const void* input_data;
+  const uint8_t* observed;
+  const void* time_steps;
+  const void* attributes;
+  const void* params;
+  const void* response_inputs;
+  void* trajectories;
+  void* last_attributes;
+  void* surprise_sum;
+  void* surprise_pointwise;
+  void* gradient;
+  void* reduced;
+  const int32_t* group;
+  double out_scale;
+  int response_fn;
+  int tangent_offset;  // this pass differentiates params [tangent_offset, tangent_offset + P)
+};
+
+}  // namespace hgf

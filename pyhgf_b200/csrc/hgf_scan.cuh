@@ -1,0 +1,174 @@
+// The time loop: one thread carries one network instance through all T
+// observations (Network.input_data's lax.scan, pyhgf/model/network.py:612-624,
+// over beliefs_propagation, pyhgf/utils/beliefs_propagation.py:24-159), with
+// the response function (pyhgf/response.py) and -- for Dual scalars -- its
+// parameter gradient fused in.  Instances are independent, so the grid is a
+// flat partition of the batch; every global access is coalesced over instances
+// (parameters [P][N], trajectories [R][T][N], outputs [.][N]); the observation
+// series is uniform across a warp (broadcast loads).
+#pragma once
+#include "hgf_ops.cuh"
+
+namespace hgf {
+
+constexpr int SCAN_THREADS = 128;
+
+// One instance, all time steps.  Returns out_scale-free summed surprise (with
+// its tangents); every per-instance output is stored here when `active`.
+template <class T, class Topo, int NSLOTS>
+HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArgs& args, long long n, bool active) {
+  using B = base_t<T>;
+  constexpr int P = scalar_traits<T>::n_tangents;
+  const Topo a(prog);
+  const long long N = args.n_instances;
+
+  // ---- initial attributes: shared vector + this instance's parameters ----
+  T s[NSLOTS];
+  const B* base = static_cast<const B*>(args.attributes);
+  const int n_slots = a.n_slots();
+  if constexpr (Topo::is_static) {
+#pragma unroll
+    for (int k = 0; k < NSLOTS; ++k)
+      if (k < n_slots) s[k] = T(HGF_LDG(base + k));
+  } else {
+    for (int k = 0; k < n_slots; ++k) s[k] = T(HGF_LDG(base + k));
+  }
+  const B* params = static_cast<const B*>(args.params);
+  for (int p = 0; p < lists.n_params; ++p) {
+    T v = T(HGF_LDG(params + static_cast<long long>(p) * N + n));
+    if constexpr (P > 0) {
+#pragma unroll
+      for (int i = 0; i < P; ++i)
+        if (i == p - args.tangent_offset) v.d[i] = B(1);
+    }
+    const int slot = lists.param_slot[p];
+    if constexpr (Topo::is_static) {
+#pragma unroll
+      for (int k = 0; k < NSLOTS; ++k)
+        if (k == slot) s[k] = v;
+    } else {
+      s[slot] = v;
+    }
+  }
+
+  const int T_steps = args.n_steps;
+  const int n_fed = a.n_fed();
+  const long long in_series = args.input_group_size > 0 ? n / args.input_group_size : 0;
+  const B* u = static_cast<const B*>(args.input_data) + in_series * T_steps * n_fed;
+  const uint8_t* obs = args.observed ? args.observed + in_series * T_steps * n_fed : nullptr;
+  const B* resp = nullptr;
+  if (args.response_inputs) {
+    const long long rs = args.response_group_size > 0 ? n / args.response_group_size : 0;
+    resp = static_cast<const B*>(args.response_inputs) + rs * T_steps;
+  }
+  const B* time_steps = static_cast<const B*>(args.time_steps);
+  B* traj = static_cast<B*>(args.trajectories);
+  B* pointwise = static_cast<B*>(args.surprise_pointwise);
+  const int response_fn = args.response_fn;
+
+  T total = T(B(0));
+  bool node1_mean_nan = false;
+
+  for (int t = 0; t < T_steps; ++t) {
+    const T dt = T(time_steps ? HGF_LDG(time_steps + t) : B(1));
+    // prediction sequence (parents before children)
+#pragma unroll (Topo::kUnroll)
+    for (int i = 0; i < a.n_pred(); ++i) apply_op(a, s, dt, a.pred_op(i), a.pred_node(i));
+    // set_observation, pyhgf/updates/observation.py:10-38
+#pragma unroll (Topo::kUnroll)
+    for (int k = 0; k < n_fed; ++k) {
+      const int node = a.input_idx(k);
+      HGF_S(node, F_MEAN) = T(HGF_LDG(u + static_cast<long long>(t) * n_fed + k));
+      HGF_S(node, F_OBSERVED) = T(obs ? static_cast<B>(HGF_LDG(obs + static_cast<long long>(t) * n_fed + k)) : B(1));
+    }
+    // prediction errors and posterior updates (children before parents)
+#pragma unroll (Topo::kUnroll)
+    for (int i = 0; i < a.n_upd(); ++i) apply_op(a, s, dt, a.upd_op(i), a.upd_node(i));
+
+    if (response_fn != RESP_NONE) {
+      const T r = response_step(a, s, response_fn, resp ? HGF_LDG(resp + t) : B(0));
+      total = total + r;
+      if (pointwise && active) pointwise[static_cast<long long>(t) * N + n] = pv(r);
+      if (response_fn == RESP_TOTAL_GAUSSIAN && a.n_nodes() > 1 && x_isnan(HGF_S(1, F_MEAN))) node1_mean_nan = true;
+    }
+    if (traj && active) {
+      if constexpr (Topo::is_static) {
+        // static record set: the four belief leaves of every node (+ the volatility-level twins)
+        int r = 0;
+#pragma unroll
+        for (int node = 0; node < a.n_nodes(); ++node) {
+#pragma unroll
+          for (int f = 0; f < 4; ++f) traj[(static_cast<long long>(r++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
+          if (a.node_type(node) == NODE_VOLATILE) {
+#pragma unroll
+            for (int f = F_MEAN_VOL; f < F_MEAN_VOL + 4; ++f) traj[(static_cast<long long>(r++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
+          }
+        }
+      } else {
+        for (int r = 0; r < lists.n_rec; ++r)
+          traj[(static_cast<long long>(r) * T_steps + t) * N + n] = pv(s[lists.rec_slot[r]]);
+      }
+    }
+  }
+
+  // response.py:87-89: total_gaussian_surprise is +inf everywhere if node 1's mean ever was NaN
+  if (response_fn == RESP_TOTAL_GAUSSIAN && node1_mean_nan) total = T(b_inf<B>());
+
+  const B scale = static_cast<B>(args.out_scale);
+  if (active) {
+    if (args.surprise_sum) static_cast<B*>(args.surprise_sum)[n] = scale * pv(total);
+    if constexpr (P > 0) {
+      if (args.gradient) {
+        B* grad = static_cast<B*>(args.gradient);
+#pragma unroll
+        for (int i = 0; i < P; ++i)
+          if (args.tangent_offset + i < lists.n_params)
+            grad[static_cast<long long>(args.tangent_offset + i) * N + n] = scale * total.d[i];
+      }
+    }
+    if (args.last_attributes) {
+      B* last = static_cast<B*>(args.last_attributes);
+      if constexpr (Topo::is_static) {
+#pragma unroll
+        for (int k = 0; k < NSLOTS; ++k)
+          if (k < a.n_nodes() * NF) last[static_cast<long long>(k) * N + n] = pv(s[k]);
+      } else {
+        for (int k = 0; k < a.n_nodes() * NF; ++k) last[static_cast<long long>(k) * N + n] = pv(s[k]);
+      }
+    }
+  }
+  return total;
+}
+
+#ifdef __CUDACC__
+// warp-aggregated atomic accumulation of per-instance sums into per-group sums
+template <class B> __device__ __forceinline__ void reduce_into_groups(B* reduced, int g, B value, bool active) {
+  const unsigned full = 0xffffffffu;
+  const int g0 = __shfl_sync(full, g, 0);
+  const bool uniform = __all_sync(full, g == g0);
+  if (uniform) {
+    B v = active ? value : B(0);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(full, v, off);
+    if ((threadIdx.x & 31) == 0) atomicAdd(reduced + g0, v);
+  } else if (active) {
+    atomicAdd(reduced + g, value);
+  }
+}
+
+template <class T, class Topo, int NSLOTS>
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLists lists, const __grid_constant__ ScanArgs args) {
+  using B = base_t<T>;
+  long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const bool active = n < args.n_instances;
+  if (!active) n = args.n_instances - 1;  // keep the warp whole for the shuffle reduction; stores are predicated
+  const T total = scan_instance<T, Topo, NSLOTS>(prog, lists, args, n, active);
+  if (args.reduced) {
+    const int g = args.group ? __ldg(args.group + n) : 0;
+    reduce_into_groups<B>(static_cast<B*>(args.reduced), g, static_cast<B>(args.out_scale) * pv(total), active);
+  }
+}
+#endif
+
+}  // namespace hgf

@@ -1,0 +1,13 @@
+#include <cstring>
+
+#include "hgf_dispatch.h"
+
+namespace hgf {
+
+const KernelVariant* select_variant(const Program& prog) {
+  for (const KernelVariant* const* v = static_variants(); *v; ++v)
+    if ((*v)->match && std::memcmp((*v)->match, &prog, sizeof(Program)) == 0) return *v;
+  return &kInterpreterVariant;
+}
+
+}  // namespace hgf
