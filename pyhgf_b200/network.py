@@ -1,0 +1,696 @@
+"""``Network`` -- the model API of the path, backed by the CUDA time loop.
+
+Mirrors the hot-path surface of ``pyhgf.model.Network``
+(pyhgf/model/network.py:85-155 constructor, :157-180 ``input_idxs``, :182-234
+``create_belief_propagation_fn``, :528-628 ``input_data``, :769-776
+``get_network``, :778-945 ``add_nodes``, :986-1022 ``surprise``, :1025-1067
+``add_edges``) with the same names, argument meaning and error behaviour.  The
+per-observation ``lax.scan`` over ``beliefs_propagation`` is replaced by one
+launch of ``libpyhgf_cuda.so`` (``hgf_filter`` / ``hgf_logp_grad``,
+include/pyhgf_cuda.h); what the reference obtains with ``jax.vmap`` over
+parameters is the native batch dimension of that launch (:meth:`Network.batch`).
+
+There is no CPU path: every method that computes needs the built library and a
+CUDA device.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from copy import deepcopy
+from typing import Callable, Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+from .topology import AdjacencyLists, Plan, get_update_sequence
+
+_COUPLING_KEYS = ("value_coupling_parents", "volatility_coupling_parents", "value_coupling_children",
+                  "volatility_coupling_children")
+_EDGE_OF_KEY = {"value_coupling_parents": "value_parents", "volatility_coupling_parents": "volatility_parents",
+                "value_coupling_children": "value_children", "volatility_coupling_children": "volatility_children"}
+
+
+# ---------------------------------------------------------------------------
+# node defaults (the state layout) -- pyhgf/model/add_nodes.py
+# ---------------------------------------------------------------------------
+def _continuous_state_defaults() -> dict:  # add_nodes.py:65-85
+    return {
+        "mean": 0.0, "expected_mean": 0.0, "precision": 1.0, "expected_precision": 1.0,
+        "volatility_coupling_children": None, "volatility_coupling_parents": None,
+        "value_coupling_children": None, "value_coupling_parents": None,
+        "tonic_volatility": -4.0, "tonic_drift": 0.0, "autoconnection_strength": 1.0, "observed": 1,
+        "temp": {"effective_precision": 0.0, "conditional_expected_precision": 1.0, "value_prediction_error": 0.0,
+                 "volatility_prediction_error": 0.0, "current_variance": 1.0},
+    }
+
+
+def _volatile_state_defaults() -> dict:  # add_nodes.py:159-184
+    return {
+        "mean": 0.0, "expected_mean": 0.0, "precision": 1.0, "expected_precision": 1.0,
+        "autoconnection_strength": 0.0,
+        "mean_vol": 0.0, "expected_mean_vol": 0.0, "precision_vol": 1.0, "expected_precision_vol": 1.0,
+        "tonic_volatility_vol": -4.0,
+        "value_coupling_children": None, "value_coupling_parents": None,
+        "temp": {"effective_precision": 0.0, "conditional_expected_precision": 1.0, "value_prediction_error": 0.0,
+                 "volatility_prediction_error": 0.0, "effective_precision_vol": 0.0, "current_variance": 1.0},
+    }
+
+
+def _binary_state_defaults() -> dict:  # add_nodes.py:330-340
+    return {
+        "observed": 1, "mean": 0, "expected_mean": 0.5, "precision": 1.0, "expected_precision": 1.0,
+        "value_coupling_parents": None, "temp": {"value_prediction_error": 0.0},
+    }
+
+
+_NODE_KINDS = {"continuous-state": (2, _continuous_state_defaults), "volatile-state": (6, _volatile_state_defaults),
+               "binary-state": (1, _binary_state_defaults)}
+_OTHER_KINDS = ("dp-state", "ef-state", "categorical-state", "constant-state")
+
+
+def get_couplings(value_parents, volatility_parents, value_children, volatility_children):
+    """Normalise coupling specifications to ``(indexes, strengths)`` tuples (add_nodes.py:603-650)."""
+    out = []
+    for indexes in (value_parents, volatility_parents, value_children, volatility_children):
+        if indexes is None:
+            out.append((None, None))
+        elif isinstance(indexes, (int, np.integer)):
+            out.append(((int(indexes),), (1.0,)))
+        elif isinstance(indexes, list):
+            out.append((tuple(indexes), tuple([1.0] * len(indexes))))
+        elif isinstance(indexes, tuple):
+            out.append((tuple(indexes[0]), tuple(indexes[1])))
+        else:
+            raise TypeError("coupling indexes should be an int, a list of ints or a tuple (indexes, strengths)")
+    return out
+
+
+def _torch_dtype(bits: int):
+    return torch.float32 if bits == 32 else torch.float64
+
+
+def _np_dtype(bits: int):
+    return np.float32 if bits == 32 else np.float64
+
+
+ParamKey = Union[tuple, str]
+
+
+class BatchResult:
+    """Outputs of one batched launch (device tensors).
+
+    ``surprise`` is the per-instance summed surprise ``[N]`` (``logp = -surprise``),
+    ``gradient[key]`` its derivative wrt a per-instance parameter ``[N]``
+    (``logp_gradient`` flips the sign), ``pointwise`` the per-trial surprise as an
+    ``[N, T]`` view, ``trajectories[(node, key)]`` ``[N, T]`` views of the recorded
+    leaves and ``last_attributes[(node, key)]`` the final state ``[N]``.
+    """
+
+    def __init__(self):
+        self.surprise = None
+        self.gradient = {}
+        self.pointwise = None
+        self.trajectories = {}
+        self.last_attributes = None
+        self.reduced = None
+        self.kernel_name = ""
+
+    def relaunch(self, stream=None):
+        """Enqueue the same evaluation again on the same device buffers (inputs and outputs stay resident
+        in HBM; a sampler or a benchmark overwrites the parameter tensors in place between calls).
+        Host cost: one C call."""
+        s = torch.cuda.current_stream(self._device) if stream is None else stream
+        if self.reduced is not None:
+            self.reduced.zero_()
+        _lib.check(self._fn(self._plan.handle, C.byref(self._call), C.c_void_p(s.cuda_stream)))
+        return self
+
+    @property
+    def logp(self):
+        return None if self.surprise is None else -self.surprise
+
+    @property
+    def logp_gradient(self):
+        return {k: -v for k, v in self.gradient.items()}
+
+
+class Network:
+    """A predictive-coding network whose belief propagation runs on a B200.
+
+    Parameters are those of ``pyhgf.model.Network`` (network.py:85-91);
+    ``dtype`` ("float32" default, as JAX; or "float64") and ``device`` are
+    additions.
+    """
+
+    def __init__(self, volatility_updates: str = "unbounded", max_posterior_precision: float = 1e10,
+                 mean_field_updates: bool = False, precision_clipping_value: float = 1e-6, dtype: str = "float32",
+                 device: Optional[Union[int, str, torch.device]] = None) -> None:
+        if volatility_updates not in ("standard", "eHGF", "unbounded"):
+            raise ValueError("Invalid update type. Should be one of the following: 'standard', 'eHGF', 'unbounded'")
+        self.edges: tuple = ()
+        self.n_nodes: int = 0
+        self.node_trajectories: Optional[dict] = None
+        self.attributes: dict = {-1: {"time_step": 0.0, "precision_clipping_value": float(precision_clipping_value)}}
+        self.last_attributes: Optional[dict] = None
+        self.update_sequence = None
+        self.scan_fn = None
+        self._input_idxs: Optional[tuple] = None
+        self.input_dim: list = []
+        self.volatility_updates = volatility_updates
+        self.max_posterior_precision = float(max_posterior_precision)
+        self.mean_field_updates = bool(mean_field_updates)
+        name = str(dtype).replace("torch.", "")
+        if name not in ("float32", "float64"):
+            raise ValueError("dtype should be 'float32' or 'float64'")
+        self.bits = 32 if name == "float32" else 64
+        self._device = device
+        self._plan: Optional[Plan] = None
+        self._plan_n_fed = None
+
+    # ------------------------------------------------------------------ graph
+    def add_nodes(self, kind: str = "continuous-state", n_nodes: int = 1, node_parameters: dict = {},
+                  value_children=None, value_parents=None, volatility_children=None, volatility_parents=None,
+                  coupling_fn: tuple = (None,), **additional_parameters):
+        """Add state node(s) (network.py:778-945; defaults add_nodes.py:65-85, 159-184, 330-340)."""
+        if kind not in _NODE_KINDS and kind not in _OTHER_KINDS:
+            raise ValueError(
+                "Invalid node type. Should be one of the following: 'dp-state', 'continuous-state', 'binary-state', "
+                "'ef-state', 'categorical-state', 'volatile-state', or 'constant-state'"
+            )
+        if kind in _OTHER_KINDS:
+            raise NotImplementedError(
+                f"'{kind}' nodes are outside the belief-propagation path this backend accelerates "
+                "(binary-, continuous- and volatile-state nodes)"
+            )
+        vp, volp, vc, volc = get_couplings(value_parents, volatility_parents, value_children, volatility_children)
+        node_type, make_defaults = _NODE_KINDS[kind]
+        if node_type == 6:  # the volatility level is implicit (add_nodes.py:106-202)
+            volp, volc = (None, None), (None, None)
+        params = make_defaults()
+        # update_parameters, add_nodes.py:653-697
+        unknown = [k for k in additional_parameters if k not in params]
+        if unknown:
+            raise ValueError(
+                f"Some parameter(s) passed as keyword arguments were not found in the default key(s) of a {kind} node "
+                f"(i.e. {list(params.keys())}). If you want to create a new key in the node's attributes, "
+                "please use the node_parameters argument instead."
+            )
+        params.update(additional_parameters)
+        params.update(node_parameters or {})
+
+        coupling_fn = tuple(coupling_fn)
+        if vc[0] is not None and len(vc[0]) != len(coupling_fn):  # insert_nodes, add_nodes.py:746-762
+            if len(coupling_fn) == 1:
+                coupling_fn = len(vc[0]) * coupling_fn
+            else:
+                raise ValueError("The number of coupling fn and value children do not match")
+
+        for _ in range(n_nodes):
+            idx = self.n_nodes
+            self.edges = self.edges + (AdjacencyLists(node_type, None, None, None, None, coupling_fn),)
+            self.attributes[idx] = deepcopy(params)
+            if vp[0] is not None:
+                for j, c in zip(*vp):
+                    self.add_edges(parent_idxs=j, children_idxs=idx, kind="value", coupling_strengths=c)
+            if vc[0] is not None:
+                for j, c in zip(*vc):
+                    self.add_edges(parent_idxs=idx, children_idxs=j, kind="value", coupling_strengths=c)
+            if volc[0] is not None:
+                for j, c in zip(*volc):
+                    self.add_edges(parent_idxs=idx, children_idxs=j, kind="volatility", coupling_strengths=c)
+            if volp[0] is not None:
+                for j, c in zip(*volp):
+                    self.add_edges(parent_idxs=j, children_idxs=idx, kind="volatility", coupling_strengths=c)
+            self.n_nodes += 1
+        self._invalidate()
+        return self
+
+    def add_edges(self, parent_idxs, children_idxs, kind: str = "value", coupling_strengths=1.0,
+                  coupling_fn: tuple = (None,)):
+        """Add value / volatility coupling(s) (network.py:1025-1067, utils/add_edges.py:10-176).
+
+        As in the reference, ``coupling_fn`` is accepted but the function in force
+        is the one the parent was created with.
+        """
+        if kind not in ("value", "volatility"):
+            raise ValueError(f"The kind of coupling should be value or volatility, got {kind}")
+        children = [children_idxs] if isinstance(children_idxs, (int, np.integer)) else list(children_idxs)
+        parents = [parent_idxs] if isinstance(parent_idxs, (int, np.integer)) else list(parent_idxs)
+        if isinstance(coupling_strengths, (int, float, np.floating, np.integer)):
+            strengths = [float(coupling_strengths)]
+        else:
+            strengths = [float(c) for c in coupling_strengths]
+        edges = list(self.edges)
+        child_field, child_key = (("value_children", "value_coupling_children") if kind == "value"
+                                  else ("volatility_children", "volatility_coupling_children"))
+        parent_field, parent_key = (("value_parents", "value_coupling_parents") if kind == "value"
+                                    else ("volatility_parents", "volatility_coupling_parents"))
+        for p in parents:
+            e = edges[p]._asdict()
+            old = self.attributes[p].get(child_key)
+            if e[child_field] is None:
+                e[child_field] = tuple(children)
+                self.attributes[p][child_key] = np.asarray(strengths, dtype=np.float64)
+            else:
+                e[child_field] = e[child_field] + tuple(children)
+                self.attributes[p][child_key] = np.concatenate([np.atleast_1d(old), strengths])
+            edges[p] = AdjacencyLists(**e)
+        for c in children:
+            e = edges[c]._asdict()
+            old = self.attributes[c].get(parent_key)
+            if e[parent_field] is None:
+                e[parent_field] = tuple(parents)
+                self.attributes[c][parent_key] = np.asarray(strengths, dtype=np.float64)
+            else:
+                e[parent_field] = e[parent_field] + tuple(parents)
+                self.attributes[c][parent_key] = np.concatenate([np.atleast_1d(old), strengths])
+            edges[c] = AdjacencyLists(**e)
+        self.edges = tuple(edges)
+        self._invalidate()
+        return self
+
+    def _invalidate(self):
+        self._plan = None
+        self.scan_fn = None
+        self.update_sequence = None
+
+    # ----------------------------------------------------------------- inputs
+    @property
+    def input_idxs(self) -> tuple:
+        """Nodes receiving observations (network.py:157-180).
+
+        Auto-detection (nodes without children) has the reference's side effect:
+        continuous input nodes get ``autoconnection_strength = tonic_volatility = 0``.
+        """
+        if self._input_idxs is not None:
+            return self._input_idxs
+        auto = tuple(i for i, e in enumerate(self.edges) if e.value_children is None and e.volatility_children is None)
+        for idx in auto:
+            if self.edges[idx].node_type == 2:
+                self.attributes[idx]["autoconnection_strength"] = 0.0
+                self.attributes[idx]["tonic_volatility"] = 0.0
+            self.attributes[idx].setdefault("observed", 1)
+        return auto
+
+    @input_idxs.setter
+    def input_idxs(self, value):
+        self._input_idxs = tuple(int(v) for v in value)
+        self._plan = None
+
+    # --------------------------------------------------------------- lowering
+    def create_belief_propagation_fn(self, overwrite: bool = True):
+        """Derive the static schedule and lower the network into a CUDA plan (network.py:182-234)."""
+        _ = self.input_idxs
+        self.input_dim = [1 for _ in self.input_idxs]
+        if self.update_sequence is None or overwrite:
+            self.update_sequence = get_update_sequence(self, self.volatility_updates, self.mean_field_updates)
+        self._plan = None
+        self._get_plan(len(self.input_idxs))
+        self.scan_fn = self._plan  # truthy marker: the "scan function" is the lowered plan
+        return self
+
+    def get_network(self):
+        """(attributes, edges, update_sequence), network.py:769-776."""
+        if self.scan_fn is None:
+            self.create_belief_propagation_fn()
+        return self.attributes, self.edges, self.update_sequence
+
+    def _get_plan(self, n_fed: int) -> Plan:
+        if self.update_sequence is None:
+            _ = self.input_idxs
+            self.update_sequence = get_update_sequence(self, self.volatility_updates, self.mean_field_updates)
+        if self._plan is None or self._plan_n_fed != n_fed:
+            self._plan = Plan(self.edges, self.update_sequence, self.input_idxs, n_fed, self.volatility_updates,
+                              self.mean_field_updates, self.max_posterior_precision)
+            self._plan_n_fed = n_fed
+        return self._plan
+
+    @property
+    def plan(self) -> Plan:
+        if self._plan is None:
+            self.create_belief_propagation_fn()
+        return self._plan
+
+    @property
+    def device(self) -> torch.device:
+        if not torch.cuda.is_available():
+            raise RuntimeError("pyhgf_b200 needs a CUDA device: the belief-propagation path has no CPU implementation")
+        d = self._device
+        if d is None:
+            return torch.device("cuda", torch.cuda.current_device())
+        if isinstance(d, int):
+            return torch.device("cuda", d)
+        return torch.device(d)
+
+    # ------------------------------------------------------- attribute vector
+    def _flatten(self, plan: Plan, attributes: Optional[dict] = None, response_parameters=None) -> np.ndarray:
+        """One instance's attribute vector in the library's slot layout (hgf_program.h)."""
+        attributes = self.attributes if attributes is None else attributes
+        v = np.zeros(plan.n_slots, dtype=np.float64)
+        for i in range(self.n_nodes):
+            a = attributes[i]
+            temp = a.get("temp", {})
+            for k, name in enumerate(_lib.FIELDS):
+                if name.startswith("temp."):
+                    val = temp.get(name[5:], 0.0)
+                else:
+                    val = a.get(name, 1.0 if name == "observed" else 0.0)
+                v[i * _lib.N_FIELDS + k] = float(val)
+            for key in _COUPLING_KEYS:
+                arr = a.get(key)
+                if arr is not None:
+                    for pos, c in enumerate(np.atleast_1d(np.asarray(arr, dtype=np.float64))):
+                        v[plan.slot(i, key, pos)] = c
+        v[plan.slot_clipping] = float(attributes[-1]["precision_clipping_value"])
+        if response_parameters is not None:
+            rp = np.atleast_1d(np.asarray(response_parameters, dtype=np.float64)).ravel()
+            if rp.size > _lib.N_RESPONSE_PARAMETERS:
+                raise ValueError(f"at most {_lib.N_RESPONSE_PARAMETERS} response-function parameters are supported")
+            v[plan.slot_response: plan.slot_response + rp.size] = rp
+        return v.astype(_np_dtype(self.bits))
+
+    def _resolve_slot(self, plan: Plan, key: ParamKey) -> int:
+        """``(node, attribute)``, ``(node, coupling_key, position)``, ``"response_parameter"`` or
+        ``("response_parameter", j)`` -> slot."""
+        if isinstance(key, str):
+            key = (key,)
+        if key[0] == "response_parameter":
+            return plan.slot(-1, "response_parameter", int(key[1]) if len(key) > 1 else 0)
+        if key[0] == "precision_clipping_value" or (key[0] == -1 and key[1] == "precision_clipping_value"):
+            return plan.slot_clipping
+        node, name = int(key[0]), key[1]
+        pos = int(key[2]) if len(key) > 2 else 0
+        return plan.slot(node, name, pos)
+
+    # ------------------------------------------------------------- the launch
+    def _format_series(self, input_data, observed, dev, grouped: bool):
+        """-> values [G, T, n_fed] on the device (+ uint8 mask or None)."""
+        dt = _torch_dtype(self.bits)
+        x = torch.as_tensor(np.asarray(input_data) if not torch.is_tensor(input_data) else input_data)
+        x = x.to(device=dev, dtype=dt, non_blocking=True)
+        if grouped:
+            if x.ndim == 2:
+                x = x[:, :, None]
+        else:
+            if x.ndim == 1:
+                x = x[:, None]
+            x = x[None]
+        if x.ndim != 3:
+            raise ValueError("input_data should be (time,), (time, inputs) or, per series, (series, time[, inputs])")
+        n_inputs = len(self.input_idxs)
+        if x.shape[2] > n_inputs:
+            raise ValueError(f"input_data has {x.shape[2]} columns but the network has {n_inputs} input node(s)")
+        obs = None
+        if observed is not None:
+            if isinstance(observed, (tuple, list)) and not grouped:
+                observed = np.stack([np.asarray(o) for o in observed], axis=1)
+            o = torch.as_tensor(np.asarray(observed) if not torch.is_tensor(observed) else observed).to(dev)
+            if grouped:
+                if o.ndim == 2:
+                    o = o[:, :, None]
+            else:
+                if o.ndim == 1:
+                    o = o[:, None]
+                o = o[None]
+            n_fed = min(x.shape[2], o.shape[2])
+            x = x[:, :, :n_fed]
+            obs = (o[:, :, :n_fed] != 0).to(torch.uint8).contiguous()
+        return x.contiguous(), obs
+
+    def _launch(self, *, values, observed, time_steps, input_group_size, n_instances, params: dict,
+                response_fn: int, response_inputs, response_group_size, response_parameters, record_slots,
+                want_last, want_sum, want_pointwise, want_grad, group, n_groups, out_scale=1.0, stream=None,
+                attributes=None):
+        L = _lib.lib()
+        dev = values.device
+        dt = _torch_dtype(self.bits)
+        n_fed = values.shape[2]
+        plan = self._get_plan(n_fed)
+        T = int(values.shape[1])
+        N = int(n_instances)
+        keep = [values]
+        call = _lib.Call()
+        call.dtype = self.bits
+        call.n_instances = N
+        call.n_steps = T
+        call.input_group_size = int(input_group_size)
+        call.input_data = values.data_ptr()
+        if observed is not None:
+            keep.append(observed)
+            call.observed = observed.data_ptr()
+        if time_steps is not None:
+            ts = torch.as_tensor(np.asarray(time_steps) if not torch.is_tensor(time_steps) else time_steps)
+            ts = ts.to(device=dev, dtype=dt).contiguous()
+            if ts.numel() != T:
+                raise ValueError("time_steps should have one entry per observation")
+            keep.append(ts)
+            call.time_steps = ts.data_ptr()
+        attr = torch.from_numpy(self._flatten(plan, attributes, response_parameters)).to(dev)
+        keep.append(attr)
+        call.attributes = attr.data_ptr()
+        keys = list(params.keys())
+        P = len(keys)
+        if P > _lib.MAX_PARAMS:
+            raise ValueError(f"at most {_lib.MAX_PARAMS} per-instance parameters per launch")
+        slots = (C.c_int32 * max(P, 1))(*[self._resolve_slot(plan, k) for k in keys])
+        call.n_params = P
+        call.param_slots = C.cast(slots, C.POINTER(C.c_int32))
+        if P:
+            cols = []
+            for k in keys:
+                col = params[k]
+                col = torch.as_tensor(np.asarray(col) if not torch.is_tensor(col) else col).to(device=dev, dtype=dt).reshape(-1)
+                if col.numel() == 1 and N != 1:
+                    col = col.expand(N)
+                if col.numel() != N:
+                    raise ValueError(f"parameter {k!r} has {col.numel()} values for {N} instances")
+                cols.append(col)
+            pmat = torch.stack(cols, 0).contiguous()
+            keep.append(pmat)
+            call.params = pmat.data_ptr()
+        call.response_fn = int(response_fn)
+        call.response_group_size = int(response_group_size)
+        if response_inputs is not None:
+            ri = torch.as_tensor(np.asarray(response_inputs) if not torch.is_tensor(response_inputs) else response_inputs)
+            ri = ri.to(device=dev, dtype=dt).contiguous()
+            if ri.shape[-1] != T:
+                raise ValueError("response_function_inputs should have one entry per observation")
+            keep.append(ri)
+            call.response_inputs = ri.data_ptr()
+        res = BatchResult()
+        res.kernel_name = plan.kernel_name
+        R = len(record_slots)
+        rec = (C.c_int32 * max(R, 1))(*record_slots)
+        traj = None
+        if R:
+            if R > _lib.MAX_RECORDS:
+                raise ValueError(f"at most {_lib.MAX_RECORDS} recorded leaves per launch")
+            traj = torch.empty((R, T, N), device=dev, dtype=dt)
+            call.n_records = R
+            call.record_slots = C.cast(rec, C.POINTER(C.c_int32))
+            call.trajectories = traj.data_ptr()
+        last = None
+        if want_last:
+            last = torch.empty((self.n_nodes * _lib.N_FIELDS, N), device=dev, dtype=dt)
+            call.last_attributes = last.data_ptr()
+        if want_sum:
+            res.surprise = torch.empty(N, device=dev, dtype=dt)
+            call.surprise_sum = res.surprise.data_ptr()
+        if want_pointwise:
+            pw = torch.empty((T, N), device=dev, dtype=dt)
+            call.surprise_pointwise = pw.data_ptr()
+            res.pointwise = pw.t()
+        grad = None
+        if want_grad:
+            grad = torch.empty((P, N), device=dev, dtype=dt)
+            call.gradient = grad.data_ptr()
+        if n_groups:
+            res.reduced = torch.zeros(n_groups, device=dev, dtype=dt)
+            call.reduced = res.reduced.data_ptr()
+            if group is not None:
+                g = torch.as_tensor(group).to(device=dev, dtype=torch.int32).contiguous()
+                keep.append(g)
+                call.group = g.data_ptr()
+        call.out_scale = float(out_scale)
+        s = torch.cuda.current_stream(dev) if stream is None else stream
+        fn = L.hgf_logp_grad if want_grad else L.hgf_filter
+        with torch.cuda.device(dev):
+            _lib.check(fn(plan.handle, C.byref(call), C.c_void_p(s.cuda_stream)))
+        for t in keep:  # inputs staged above must outlive the (asynchronous) kernel
+            if t.is_cuda:
+                t.record_stream(s)
+        # everything a relaunch needs stays referenced by the result (BatchResult.relaunch)
+        res._call, res._fn, res._plan, res._keep, res._device = call, fn, plan, (keep, slots, rec), dev
+        res._traj = traj
+        res._last = last
+        if grad is not None:
+            res.gradient = {k: grad[i] for i, k in enumerate(keys)}
+            res._grad = grad
+        return res, plan
+
+    # ------------------------------------------------------------ input_data
+    def input_data(self, input_data, time_steps=None, observed=None, input_idxs=None, rng_keys=None,
+                   record_trajectories: bool = True):
+        """Filter one observation series (network.py:528-628).
+
+        ``input_data`` is ``(time,)`` or ``(time, n_inputs)``.  Every call restarts
+        from ``self.attributes``.  Populates ``node_trajectories`` (NumPy arrays of
+        length ``time`` per node attribute) and ``last_attributes``.
+        """
+        if rng_keys is not None:
+            raise NotImplementedError("rng_keys only serve action functions, which are outside the accelerated path")
+        if input_idxs is not None:
+            self.input_idxs = input_idxs
+        if self.scan_fn is None:
+            self.create_belief_propagation_fn()
+        dev = self.device
+        values, obs = self._format_series(input_data, observed, dev, grouped=False)
+        plan = self._get_plan(values.shape[2])
+        T = values.shape[1]
+        record = list(range(self.n_nodes * _lib.N_FIELDS)) if record_trajectories else []
+        res, plan = self._launch(values=values, observed=obs, time_steps=time_steps, input_group_size=0, n_instances=1,
+                                 params={}, response_fn=0, response_inputs=None, response_group_size=0,
+                                 response_parameters=None, record_slots=record, want_last=True, want_sum=False,
+                                 want_pointwise=False, want_grad=False, group=None, n_groups=0)
+        last = res._last[:, 0].double().cpu().numpy()
+        ts = np.ones(T) if time_steps is None else np.asarray(time_steps, dtype=np.float64)
+        self.last_attributes = self._unflatten(last, float(ts[-1]) if T else 0.0)
+        if record_trajectories:
+            traj = res._traj[:, :, 0].cpu().numpy()  # [R, T]
+            nt = {}
+            for i in range(self.n_nodes):
+                a = self.attributes[i]
+                d, temp = {}, {}
+                for k, name in enumerate(_lib.FIELDS):
+                    col = traj[i * _lib.N_FIELDS + k]
+                    if name.startswith("temp."):
+                        if name[5:] in a.get("temp", {}):
+                            temp[name[5:]] = col
+                    elif name in a:
+                        d[name] = col
+                for key in _COUPLING_KEYS:
+                    if key in a:
+                        d[key] = None if a[key] is None else np.broadcast_to(
+                            np.asarray(a[key], dtype=traj.dtype), (T, np.size(a[key])))
+                d["temp"] = temp
+                nt[i] = d
+            nt[-1] = {"time_step": ts.astype(traj.dtype),
+                      "precision_clipping_value": np.full(T, self.attributes[-1]["precision_clipping_value"], dtype=traj.dtype)}
+            self.node_trajectories = nt
+        else:
+            self.node_trajectories = None
+        self._last_inputs = (input_data, time_steps, observed)
+        return self
+
+    def _unflatten(self, vec: np.ndarray, time_step: float) -> dict:
+        out = deepcopy(self.attributes)
+        cast = _np_dtype(self.bits)
+        for i in range(self.n_nodes):
+            for k, name in enumerate(_lib.FIELDS):
+                val = cast(vec[i * _lib.N_FIELDS + k])
+                if name.startswith("temp."):
+                    if name[5:] in out[i].get("temp", {}):
+                        out[i]["temp"][name[5:]] = val
+                elif name in out[i]:
+                    out[i][name] = val
+        out[-1]["time_step"] = time_step
+        return out
+
+    # --------------------------------------------------------------- surprise
+    def surprise(self, response_function: Callable, response_function_inputs=(), response_function_parameters=None):
+        """Per-trial surprise under a response function (network.py:986-1022)."""
+        return response_function(hgf=self, response_function_inputs=response_function_inputs,
+                                 response_function_parameters=response_function_parameters)
+
+    def _fused_response(self, name: str, response_function_inputs=None, response_function_parameters=None) -> np.ndarray:
+        """Per-trial surprise of a built-in response function for the series last given to ``input_data``:
+        the filter is re-run with the response fused into the time loop (no trajectory is materialised)."""
+        if getattr(self, "_last_inputs", None) is None:
+            raise RuntimeError("call input_data() before surprise()")
+        input_data, time_steps, observed = self._last_inputs
+        dev = self.device
+        values, obs = self._format_series(input_data, observed, dev, grouped=False)
+        ri = None
+        if response_function_inputs is not None and np.size(response_function_inputs) > 0:
+            ri = np.asarray(response_function_inputs).reshape(1, -1)
+        res, _ = self._launch(values=values, observed=obs, time_steps=time_steps, input_group_size=0, n_instances=1,
+                              params={}, response_fn=_lib.RESPONSES[name], response_inputs=ri, response_group_size=0,
+                              response_parameters=response_function_parameters, record_slots=[], want_last=False,
+                              want_sum=False, want_pointwise=True, want_grad=False, group=None, n_groups=0)
+        return res.pointwise[0].cpu().numpy()
+
+    # ------------------------------------------------------------------ batch
+    def batch(self, input_data, parameters: Optional[dict] = None, *, response_function=None,
+              response_function_inputs=None, response_function_parameters=None, time_steps=None, observed=None,
+              n_instances: Optional[int] = None, input_group_size: int = 0, response_group_size: int = 0,
+              record: Sequence[tuple] = (), last_attributes: bool = False, pointwise: bool = False,
+              gradient: bool = False, group=None, n_groups: int = 0, out_scale: float = 1.0, stream=None) -> BatchResult:
+        """Run N independent instances of this network in one launch.
+
+        What the reference writes as ``jax.vmap(lambda p: Network()...input_data(u).surprise(f).sum())(params)``
+        (and ``jax.grad`` of it) -- notebooks 3-Multilevel_HGF / 4-Parameter_recovery.
+
+        parameters : ``{key: array[N]}`` per-instance overrides of the attribute vector; a key is
+            ``(node, "tonic_volatility")``, ``(node, "volatility_coupling_children", k)`` or
+            ``("response_parameter", j)``.
+        input_data : one series ``(T[, n_inputs])`` shared by all instances, or with
+            ``input_group_size = g`` a stack ``(G, T[, n_inputs])`` where instance n reads series ``n // g``.
+        response_function : one of ``pyhgf_b200.response``'s functions (or its name): fused into the time loop.
+        record : ``[(node, attribute), ...]`` leaves to record at every step -> ``result.trajectories``.
+        gradient : also return d(surprise)/d(parameters) (``hgf_logp_grad``).
+        group / n_groups : sum ``out_scale * surprise`` of the instances of each group (e.g. chain) on the device.
+        """
+        parameters = dict(parameters or {})
+        if self.scan_fn is None:
+            self.create_belief_propagation_fn()
+        dev = self.device
+        grouped = input_group_size > 0
+        values, obs = self._format_series(input_data, observed, dev, grouped=grouped)
+        if n_instances is None:
+            sizes = {int(np.size(v)) if not torch.is_tensor(v) else int(v.numel()) for v in parameters.values()} - {1}
+            if len(sizes) > 1:
+                raise ValueError(f"per-instance parameters disagree on the batch size: {sorted(sizes)}")
+            n_instances = sizes.pop() if sizes else (values.shape[0] * input_group_size if grouped else 1)
+        if grouped and values.shape[0] * input_group_size < n_instances:
+            raise ValueError("not enough input series for n_instances / input_group_size")
+        name = response_function if (response_function is None or isinstance(response_function, str)) else getattr(
+            response_function, "_hgf_response", None)
+        if response_function is not None and name not in _lib.RESPONSES:
+            raise NotImplementedError(
+                "only the built-in response functions of pyhgf_b200.response are fused into the kernel; for a custom "
+                "callable, record the trajectories it needs (record=[...]) and apply it to result.trajectories"
+            )
+        plan = self._get_plan(values.shape[2])
+        rec_slots = [self._resolve_slot(plan, k) for k in record]
+        ri = response_function_inputs
+        if ri is not None and np.size(ri) == 0:
+            ri = None
+        if ri is not None:
+            ri = torch.as_tensor(np.asarray(ri) if not torch.is_tensor(ri) else ri)
+            if ri.ndim == 1:
+                ri = ri[None]
+        res, plan = self._launch(values=values, observed=obs, time_steps=time_steps, input_group_size=input_group_size,
+                                 n_instances=n_instances, params=parameters, response_fn=_lib.RESPONSES[name],
+                                 response_inputs=ri, response_group_size=response_group_size,
+                                 response_parameters=response_function_parameters, record_slots=rec_slots,
+                                 want_last=last_attributes, want_sum=name is not None, want_pointwise=pointwise and name is not None,
+                                 want_grad=gradient, group=group, n_groups=n_groups, out_scale=out_scale, stream=stream)
+        if rec_slots:
+            res.trajectories = {tuple(k): res._traj[i].t() for i, k in enumerate(record)}
+        if last_attributes:
+            res.last_attributes = _LastAttributes(res._last, plan, self)
+        return res
+
+
+class _LastAttributes:
+    """``[(node, key)] -> tensor[N]`` view of the final attribute vectors."""
+
+    def __init__(self, flat, plan, net):
+        self.flat, self._plan, self._net = flat, plan, net
+
+    def __getitem__(self, key):
+        node, name = key
+        f = _lib.FIELD_INDEX[name] if name in _lib.FIELD_INDEX else _lib.FIELD_INDEX["temp." + name]
+        return self.flat[node * _lib.N_FIELDS + f]

@@ -1,0 +1,429 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle and with the reference's goldens.
+
+Tolerances (BASELINE.json north_star): float32, <= 1e-5 relative on per-trial means and precisions,
+<= 1e-4 relative on summed surprise / logp and on gradients (well-conditioned parameter sets; the
+saturating regimes of SURVEY.md §4 are finite/order-of-magnitude checks).  float64 launches are held to
+1e-9.  Everything here needs a B200: run with ``-m gpu``.
+"""
+
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import nets
+from oracle import network as onet
+
+pytestmark = pytest.mark.gpu
+
+RTOL_TRAJ = 1e-5
+RTOL_SUM = 1e-4
+
+
+@pytest.fixture(scope="module")
+def G():
+    import torch
+
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from pyhgf_b200 import _lib
+
+    _lib.lib()  # the CUDA library must be present: there is no fallback to skip to
+    import pyhgf_b200.network as g
+
+    return g
+
+
+@pytest.fixture(scope="module")
+def R():
+    from pyhgf_b200 import response
+
+    return response
+
+
+def assert_traj_close(gnet, onet_, nodes, rtol, atol=1e-7, keys=nets.BELIEFS):
+    for node in nodes:
+        for k in keys:
+            a = np.asarray(gnet.node_trajectories[node][k], dtype=np.float64)
+            b = np.asarray(onet_.node_trajectories[node][k], dtype=np.float64)
+            assert a.shape == b.shape
+            assert np.array_equal(np.isnan(a), np.isnan(b)), (node, k)
+            ok = np.isclose(a, b, rtol=rtol, atol=atol, equal_nan=True)
+            assert ok.all(), (node, k, float(np.nanmax(np.abs(a - b) / (np.abs(b) + atol))))
+
+
+# ------------------------------------------------------------------ reference goldens, straight on the GPU
+def test_golden_binary_one_step(G):  # tests/test_binary.py:30-70
+    net = (G.Network().add_nodes(kind="binary-state").add_nodes(value_children=0, mean=1.0, tonic_volatility=1.0)
+           .add_nodes(volatility_children=1, mean=1.0, tonic_volatility=1.0).input_data(np.ones(1)))
+    a = net.last_attributes
+    for k, v in zip(["mean", "expected_mean", "expected_precision"], [1.0, 0.7310586, 0.19661193]):
+        assert np.isclose(a[0][k], v, rtol=1e-5)
+    for k, v in zip(["mean", "expected_mean", "precision", "expected_precision"], [2.2378633, 1.0, 0.21726260, 0.02065066]):
+        assert np.isclose(a[1][k], v, rtol=1e-5)
+    for k, v in zip(["mean", "expected_mean", "precision", "expected_precision"], [0.37627372, 1.0, 0.39340553, 0.26894143]):
+        assert np.isclose(a[2][k], v, rtol=1e-5)
+
+
+def test_golden_binary_scan(G, datasets):  # tests/test_binary.py:73-94
+    net = nets.binary3(G.Network).input_data(datasets["u"])
+    for k, v in zip(nets.BELIEFS, [-2.3191204, -2.171629, 0.6937843, 0.6019279]):
+        assert np.isclose(net.node_trajectories[1][k][-1], v, rtol=1e-5)
+    for k, v in zip(nets.BELIEFS, [2.478936, 2.4795845, 1.7116449, 1.6612335]):
+        assert np.isclose(net.node_trajectories[2][k][-1], v, rtol=1e-5)
+
+
+def test_golden_continuous_scan(G, datasets):  # tests/test_continuous.py:101-131
+    net = nets.continuous2(G.Network).input_data(datasets["x"])
+    for node, vals in {0: [0.8241, 0.7945459, 1.0, 0.7623690], 1: [0.7978380, 0.7945459, 6.8440757, 6.0817065],
+                       2: [-2.2633543, -2.2633660, 1.4760352, 1.4371926]}.items():
+        for k, v in zip(nets.BELIEFS, vals):
+            assert np.isclose(net.node_trajectories[node][k][-1], v, rtol=1e-5), (node, k)
+
+
+def test_golden_surprises(G, R, datasets):  # tests/test_model.py:113-268, tests/test_responses.py:10-50, README.md:115
+    x, u, y = datasets["x"], datasets["u"], datasets["y"]
+    two = (G.Network().add_nodes(precision=1e4)
+           .add_nodes(value_children=([0], [1.0]), node_parameters={"mean": x[0], "precision": 1e4, "tonic_volatility": -3.0, "tonic_drift": 0.0})
+           .add_nodes(volatility_children=([1], [1.0]), node_parameters={"mean": 0.0, "precision": 1e1, "tonic_volatility": -3.0, "tonic_drift": 0.0})
+           .input_data(x))
+    assert np.isclose(two.surprise(R.first_level_gaussian_surprise).sum(), -1924.7515, rtol=1e-5)
+    three = nets.continuous3(G.Network).input_data(x)
+    assert np.isclose(three.surprise(R.first_level_gaussian_surprise).sum(), -2034.3989, rtol=1e-5)
+    assert np.isclose(R.total_gaussian_surprise(three).sum(), -2535.604, rtol=1e-5)
+    b2 = (G.Network().add_nodes(kind="binary-state", node_parameters={"mean": 0.0, "precision": 0.0})
+          .add_nodes(value_children=([0], [1.0]), node_parameters={"mean": 0.5, "precision": 1e4, "tonic_volatility": -6.0, "tonic_drift": 0.0})
+          .input_data(u))
+    assert np.isclose(b2.surprise(R.first_level_binary_surprise).sum(), 215.58821, rtol=1e-5)
+    soft = (G.Network().add_nodes(kind="binary-state", node_parameters={"mean": 0.5, "precision": 0.0})
+            .add_nodes(value_children=([0], [1.0]), node_parameters={"mean": 0.0, "precision": 1.0, "tonic_volatility": -6.0, "tonic_drift": 0.0})
+            .input_data(u))
+    assert np.isclose(soft.surprise(R.binary_softmax, response_function_inputs=y).sum(), 195.81573, rtol=1e-5)
+    s = soft.surprise(R.binary_softmax_inverse_temperature, response_function_inputs=y, response_function_parameters=2.0)
+    assert np.isclose(s.sum(), 188.77818, rtol=1e-5)
+    readme = nets.binary2(G.Network).input_data(u)
+    s = readme.surprise(R.binary_softmax_inverse_temperature, response_function_inputs=y, response_function_parameters=4.0)
+    assert np.isclose(s.sum(), 138.8992462158203, rtol=1e-5)
+
+
+def test_saturating_binary_is_finite(G, R, datasets):  # tests/test_model.py:237-268: rounding-sensitive at the 1 % level
+    three = (G.Network().add_nodes(kind="binary-state", node_parameters={"mean": 0.0, "precision": 0.0})
+             .add_nodes(value_children=([0], [1.0]), node_parameters={"mean": 0.5, "precision": 1e4, "tonic_volatility": -6.0, "tonic_drift": 0.0})
+             .add_nodes(volatility_children=([1], [1.0]), node_parameters={"mean": 0.0, "precision": 1e1, "tonic_volatility": -2.0, "tonic_drift": 0.0})
+             .input_data(datasets["u"]))
+    s = three.surprise(R.first_level_binary_surprise).sum()
+    assert np.isfinite(s) and 0.9 * 1242.3856 < s < 1.1 * 1256.755
+
+
+# ------------------------------------------------------------------ full trajectories vs the oracle
+CASES = [
+    ("binary3", nets.binary3, "u", {}),
+    ("binary2", nets.binary2, "u", {}),
+    ("continuous2", nets.continuous2, "x", {}),
+    ("continuous3", nets.continuous3, "x", {}),
+    ("volatile2", nets.volatile2, "x", {}),
+    ("tanh", nets.tanh_coupling, "x", {}),
+    ("multi_child", nets.multi_child, "ar2", {}),
+    ("ghgf16", nets.ghgf16, "ar4", {}),
+]
+for vu in ("standard", "eHGF"):
+    for mf in (False, True):
+        CASES.append((f"continuous2-{vu}-mf{int(mf)}", nets.continuous2, "x", dict(volatility_updates=vu, mean_field_updates=mf)))
+        CASES.append((f"volatile2-{vu}-mf{int(mf)}", nets.volatile2, "x", dict(volatility_updates=vu, mean_field_updates=mf)))
+CASES.append(("continuous2-unbounded-mf1", nets.continuous2, "x", dict(mean_field_updates=True)))
+CASES.append(("binary3-ehgf", nets.binary3, "u", dict(volatility_updates="eHGF")))
+
+
+def _series(name, datasets):
+    if name in ("u", "x"):
+        return datasets[name]
+    return nets.ar1_series(400, n_series=int(name[2:]))
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_trajectories_match_oracle(G, datasets, case, dtype):
+    _, build, series, kw = case
+    data = _series(series, datasets)
+    g = build(G.Network, dtype=dtype, **kw).input_data(data)
+    o = build(onet.Network, dtype=dtype, **kw).input_data(data)
+    rtol = RTOL_TRAJ if dtype == "float32" else 1e-9
+    keys = nets.BELIEFS
+    assert_traj_close(g, o, range(g.n_nodes), rtol, atol=1e-6 if dtype == "float32" else 1e-12, keys=keys)
+    for node, e in enumerate(g.edges):
+        if e.node_type == 6:
+            assert_traj_close(g, o, [node], rtol, atol=1e-6 if dtype == "float32" else 1e-12,
+                              keys=("mean_vol", "expected_mean_vol", "precision_vol", "expected_precision_vol"))
+    # the reference's record_trajectories=False contract (tests/test_continuous.py:134-165)
+    g2 = build(G.Network, dtype=dtype, **kw).input_data(data, record_trajectories=False)
+    assert g2.node_trajectories is None
+    for node in range(g.n_nodes):
+        for k in ("mean", "precision"):
+            assert g2.last_attributes[node][k] == g.last_attributes[node][k]
+            assert g.last_attributes[node][k] == g.node_trajectories[node][k][-1]
+
+
+def test_time_steps_and_missing_observations(G, datasets):
+    rng = np.random.default_rng(3)
+    x = datasets["x"][:200]
+    ts = rng.uniform(0.5, 2.0, size=200)
+    obs = (rng.uniform(size=200) > 0.2).astype(int)
+    for vu in ("unbounded", "eHGF", "standard"):
+        g = nets.continuous2(G.Network, volatility_updates=vu).input_data(x, time_steps=ts, observed=obs)
+        o = nets.continuous2(onet.Network, volatility_updates=vu).input_data(x, time_steps=ts, observed=obs)
+        assert_traj_close(g, o, range(3), RTOL_TRAJ, atol=1e-6)
+    u = datasets["u"]
+    obs = (rng.uniform(size=320) > 0.3).astype(int)
+    g = nets.binary3(G.Network).input_data(u, observed=obs)
+    o = nets.binary3(onet.Network).input_data(u, observed=obs)
+    assert_traj_close(g, o, range(3), RTOL_TRAJ, atol=1e-6)
+
+
+def test_nan_propagates_like_the_reference(G, R):
+    # omega so large that exp overflows: the reference signals in-band (NaN beliefs -> +inf surprise)
+    data = np.array([0.0, 1.0] * 20)
+    g = nets.binary3(G.Network, om2=80.0, om3=80.0).input_data(data)
+    o = nets.binary3(onet.Network, om2=80.0, om3=80.0).input_data(data)
+    for node in range(3):
+        for k in nets.BELIEFS:
+            a, b = g.node_trajectories[node][k], o.node_trajectories[node][k]
+            assert np.array_equal(np.isnan(a), np.isnan(b)), (node, k)
+            assert np.array_equal(np.isinf(a), np.isinf(b)), (node, k)
+    sg = g.surprise(R.first_level_binary_surprise)
+    so = o.surprise(onet.first_level_binary_surprise)
+    assert np.array_equal(np.isinf(sg), np.isinf(so))
+
+
+# ------------------------------------------------------------------ batched surprise and gradients
+def _grid(n, lo=-7.0, hi=-1.0, seed=0):
+    rng = np.random.default_rng(seed)
+    return rng.uniform(lo, hi, size=n)
+
+
+@pytest.mark.parametrize("n", [1, 31, 128, 1000])
+def test_batched_binary_logp_matches_oracle(G, R, datasets, n):
+    u, y = datasets["u"], datasets["y"]
+    om2, om3, temp = _grid(n, -6, -1, 1), _grid(n, -6, -1, 2), np.exp(_grid(n, -0.5, 1.0, 3))
+    g = nets.binary3(G.Network)
+    res = g.batch(u, {(1, "tonic_volatility"): om2, (2, "tonic_volatility"): om3, ("response_parameter", 0): temp},
+                  response_function=R.binary_softmax_inverse_temperature, response_function_inputs=y, pointwise=True,
+                  last_attributes=True, record=[(1, "mean"), (2, "precision")])
+    o = nets.binary3(onet.Network).create_belief_propagation_fn()
+    slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
+    want, last = o.batch_surprise(u, slots, np.stack([om2, om3, temp]), "binary_softmax_inverse_temperature",
+                                  resp_inputs=y, return_last=True)
+    got = res.surprise.double().cpu().numpy()
+    assert np.allclose(got, want, rtol=RTOL_SUM)
+    assert np.allclose(res.pointwise.sum(1).double().cpu().numpy(), want, rtol=RTOL_SUM)
+    assert tuple(res.pointwise.shape) == (n, 320)
+    assert np.allclose(res.last_attributes[(1, "mean")].double().cpu().numpy(), last[:, o.slot(1, "mean")], rtol=RTOL_TRAJ, atol=1e-6)
+    assert np.allclose(res.trajectories[(1, "mean")][:, -1].double().cpu().numpy(), last[:, o.slot(1, "mean")], rtol=RTOL_TRAJ, atol=1e-6)
+    assert np.allclose(res.trajectories[(2, "precision")][:, -1].double().cpu().numpy(), last[:, o.slot(2, "precision")], rtol=RTOL_TRAJ)
+
+
+def test_batched_continuous_logp_matches_oracle(G, R, datasets):
+    x = datasets["x"]
+    n = 777
+    rng = np.random.default_rng(0)
+    om = [np.clip(rng.normal(m, 1.0, n), m - 3, m + 3) for m in (-13.0, -2.0, -2.0)]
+    g = nets.continuous3(G.Network)
+    res = g.batch(x, {(1, "tonic_volatility"): om[0], (2, "tonic_volatility"): om[1], (3, "tonic_volatility"): om[2]},
+                  response_function=R.first_level_gaussian_surprise)
+    o = nets.continuous3(onet.Network).create_belief_propagation_fn()
+    slots = [o.slot(i, "tonic_volatility") for i in (1, 2, 3)]
+    want = o.batch_surprise(x, slots, np.stack(om), "first_level_gaussian_surprise")
+    got = res.surprise.double().cpu().numpy()
+    finite = np.isfinite(want)
+    assert np.array_equal(finite, np.isfinite(got))
+    assert np.allclose(got[finite], want[finite], rtol=RTOL_SUM, atol=1e-2)  # sums cross zero: ~2e3 magnitude terms
+
+
+@pytest.mark.parametrize("dtype,rtol", [("float64", 1e-7), ("float32", RTOL_SUM)])
+def test_gradient_matches_dual_oracle(G, R, datasets, dtype, rtol):
+    u, y = datasets["u"], datasets["y"]
+    n = 200
+    om2, om3, temp = _grid(n, -5, -2, 1), _grid(n, -5, -2, 2), np.exp(_grid(n, -0.3, 0.8, 3))
+    mean1 = _grid(n, -0.5, 0.5, 4)
+    g = nets.binary3(G.Network, dtype=dtype)
+    keys = [(1, "tonic_volatility"), (2, "tonic_volatility"), ("response_parameter", 0), (1, "mean"), (2, "precision")]
+    vals = [om2, om3, temp, mean1, np.exp(_grid(n, -0.5, 0.5, 5))]
+    res = g.batch(u, dict(zip(keys, vals)), response_function=R.binary_softmax_inverse_temperature,
+                  response_function_inputs=y, gradient=True)
+    o = nets.binary3(onet.Network, dtype=dtype).create_belief_propagation_fn()
+    slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0),
+             o.slot(1, "mean"), o.slot(2, "precision")]
+    p = np.stack(vals)
+    if dtype == "float32":
+        p = p.astype(np.float32).astype(np.float64)
+    want_s, want_g = o.batch_grad(u, slots, p, "binary_softmax_inverse_temperature", resp_inputs=y)
+    assert np.allclose(res.surprise.double().cpu().numpy(), want_s, rtol=rtol)
+    for i, k in enumerate(keys):
+        got = res.gradient[k].double().cpu().numpy()
+        scale = np.abs(want_g[i]).max()
+        assert np.allclose(got, want_g[i], rtol=rtol * (10 if dtype == "float32" else 1), atol=rtol * scale), (k, np.abs(got - want_g[i]).max(), scale)
+
+
+def test_gradient_continuous_and_coupling(G, R, datasets):
+    x = datasets["x"][:300]
+    n = 64
+    g = nets.continuous3(G.Network, dtype="float64")
+    keys = [(1, "tonic_volatility"), (2, "tonic_volatility"), (3, "tonic_volatility"), (2, "volatility_coupling_children", 0),
+            (1, "volatility_coupling_parents", 0), (2, "tonic_drift")]
+    vals = [_grid(n, -12, -9, 1), _grid(n, -3, -1, 2), _grid(n, -3, -1, 3), _grid(n, 0.8, 1.2, 4), _grid(n, 0.8, 1.2, 5),
+            _grid(n, -0.01, 0.01, 6)]
+    res = g.batch(x, dict(zip(keys, vals)), response_function=R.first_level_gaussian_surprise, gradient=True)
+    o = nets.continuous3(onet.Network, dtype="float64").create_belief_propagation_fn()
+    slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(3, "tonic_volatility"),
+             o.slot(2, "volatility_coupling_children", 0), o.slot(1, "volatility_coupling_parents", 0), o.slot(2, "tonic_drift")]
+    want_s, want_g = o.batch_grad(x, slots, np.stack(vals), "first_level_gaussian_surprise")
+    assert np.allclose(res.surprise.cpu().numpy(), want_s, rtol=1e-8)
+    for i, k in enumerate(keys):
+        got = res.gradient[k].cpu().numpy()
+        assert np.allclose(got, want_g[i], rtol=1e-6, atol=1e-7 * np.abs(want_g[i]).max()), k
+
+
+def test_grouped_series_and_chain_reduction(G, R):
+    """Config 4's layout: participants x chains, per-participant series, per-chain sums reduced on the device."""
+    rng = np.random.default_rng(5)
+    n_part, n_chain, T = 6, 5, 120
+    u = (rng.uniform(size=(n_part, T)) > 0.5).astype(float)
+    y = (rng.uniform(size=(n_part, T)) > 0.5).astype(float)
+    n = n_part * n_chain
+    om2, om3, temp = _grid(n, -5, -2, 1), _grid(n, -5, -2, 2), np.exp(_grid(n, -0.3, 0.8, 3))
+    import torch
+
+    group = torch.arange(n, dtype=torch.int32) % n_chain
+    g = nets.binary3(G.Network)
+    res = g.batch(u, {(1, "tonic_volatility"): om2, (2, "tonic_volatility"): om3, ("response_parameter", 0): temp},
+                  response_function=R.binary_softmax_inverse_temperature, response_function_inputs=y,
+                  input_group_size=n_chain, response_group_size=n_chain, group=group, n_groups=n_chain, out_scale=-1.0,
+                  gradient=True)
+    o = nets.binary3(onet.Network).create_belief_propagation_fn()
+    slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
+    want = o.batch_surprise(u, slots, np.stack([om2, om3, temp]), "binary_softmax_inverse_temperature", resp_inputs=y,
+                            group_size=n_chain)
+    logp = res.surprise.double().cpu().numpy()  # out_scale = -1
+    assert np.allclose(logp, -want, rtol=RTOL_SUM)
+    per_chain = -want.reshape(n_part, n_chain).sum(0)
+    assert np.allclose(res.reduced.double().cpu().numpy(), per_chain, rtol=RTOL_SUM)
+
+
+def test_distribution_op(G, R, datasets):
+    from pyhgf_b200.distribution import HGFDistribution, HGFPointwise
+
+    u, y = datasets["u"], datasets["y"]
+    op = HGFDistribution(n_levels=2, model_type="binary", input_data=u[None, :], response_function=R.binary_softmax,
+                         response_function_inputs=y[None, :])
+    # tests/test_responses.py:10-30 -- omega_2 = -6 gives 195.81573 with the default initial beliefs
+    assert np.isclose(float(op(tonic_volatility_2=-6.0)), -195.81573, rtol=1e-5)
+    n = 9
+    uu = np.repeat(u[None, :], n, 0)
+    yy = np.repeat(y[None, :], n, 0)
+    om2 = np.linspace(-6, -2, n)
+    op3 = HGFDistribution(n_levels=3, model_type="binary", input_data=uu, response_function=R.binary_softmax_inverse_temperature,
+                          response_function_inputs=yy)
+    total, grads = op3.value_and_grad(tonic_volatility_2=om2, response_function_parameters=np.full(n, 2.0))
+    o = nets.binary3(onet.Network).create_belief_propagation_fn()
+    slots = [o.slot(1, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
+    want_s, want_g = o.batch_grad(u, slots, np.stack([om2, np.full(n, 2.0)]), "binary_softmax_inverse_temperature", resp_inputs=y)
+    assert np.isclose(float(total), -want_s.sum(), rtol=RTOL_SUM)
+    assert np.allclose(grads["tonic_volatility_2"].double().cpu().numpy(), -want_g[0], rtol=1e-3, atol=1e-4 * np.abs(want_g[0]).max())
+    pw = HGFPointwise(n_levels=3, model_type="binary", input_data=uu, response_function=R.binary_softmax_inverse_temperature,
+                      response_function_inputs=yy)(tonic_volatility_2=om2, response_function_parameters=np.full(n, 2.0))
+    assert tuple(pw.shape) == (n, 320)
+    assert np.allclose(pw.sum(1).double().cpu().numpy(), -want_s, rtol=RTOL_SUM)
+
+
+# ------------------------------------------------------------------ the C ABI with host buffers
+def test_c_abi_host_entry_point(G, datasets):
+    from pyhgf_b200 import _lib
+
+    u = datasets["u"].astype(np.float32)
+    net = nets.binary3(G.Network)
+    net.create_belief_propagation_fn()
+    plan = net.plan
+    n = 300
+    om2 = _grid(n, -6, -1, 1).astype(np.float32)
+    attr = net._flatten(plan)
+    slots = (C.c_int32 * 1)(plan.slot(1, "tonic_volatility"))
+    out = np.zeros(n, np.float32)
+    call = _lib.Call()
+    call.dtype, call.n_instances, call.n_steps = 32, n, 320
+    call.input_data = u.ctypes.data
+    call.attributes = attr.ctypes.data
+    call.n_params, call.param_slots, call.params = 1, C.cast(slots, C.POINTER(C.c_int32)), om2.ctypes.data
+    call.response_fn = _lib.RESPONSES["first_level_binary_surprise"]
+    call.surprise_sum = out.ctypes.data
+    call.out_scale = 1.0
+    before = _lib.launch_count()
+    _lib.check(_lib.lib().hgf_filter_host(plan.handle, C.byref(call), 0))
+    assert _lib.launch_count() == before + 1
+    o = nets.binary3(onet.Network).create_belief_propagation_fn()
+    want = o.batch_surprise(u, [o.slot(1, "tonic_volatility")], om2[None, :], "first_level_binary_surprise")
+    assert np.allclose(out, want, rtol=RTOL_SUM)
+    # invalid arguments are errors, not crashes
+    call.n_params = 99
+    assert _lib.lib().hgf_filter_host(plan.handle, C.byref(call), 0) != 0
+    assert b"n_params" in _lib.lib().hgf_last_error()
+
+
+def test_empty_batch_and_empty_series(G, R, datasets):
+    g = nets.binary3(G.Network)
+    res = g.batch(datasets["u"], {(1, "tonic_volatility"): np.zeros(0)}, response_function=R.first_level_binary_surprise,
+                  n_instances=0)
+    assert res.surprise.numel() == 0
+    res = g.batch(np.zeros(0), {(1, "tonic_volatility"): np.array([-3.0, -4.0])}, response_function=R.first_level_binary_surprise)
+    assert np.array_equal(res.surprise.cpu().numpy(), np.zeros(2, np.float32))
+
+
+# ------------------------------------------------------------------ full-size properties (BASELINE configs)
+def test_config3_grid_properties(G, R, datasets):
+    """1M-point omega grid x 320 trials: spot rows against the oracle, determinism, permutation equivariance."""
+    import torch
+
+    u = datasets["u"]
+    side = 1024
+    om2 = np.repeat(np.linspace(-8, 0, side), side)
+    om3 = np.tile(np.linspace(-8, 0, side), side)
+    g = nets.binary3(G.Network)
+    p = {(1, "tonic_volatility"): torch.as_tensor(om2, dtype=torch.float32, device="cuda"),
+         (2, "tonic_volatility"): torch.as_tensor(om3, dtype=torch.float32, device="cuda")}
+    a = g.batch(u, p, response_function=R.first_level_binary_surprise).surprise
+    b = g.batch(u, p, response_function=R.first_level_binary_surprise).surprise
+    assert torch.equal(a, b) or torch.equal(torch.nan_to_num(a), torch.nan_to_num(b))
+    perm = torch.randperm(side * side, device="cuda")
+    c = g.batch(u, {k: v[perm] for k, v in p.items()}, response_function=R.first_level_binary_surprise).surprise
+    assert torch.equal(torch.nan_to_num(a[perm], nan=-1.0), torch.nan_to_num(c, nan=-1.0))
+    idx = np.random.default_rng(0).choice(side * side, 512, replace=False)
+    o = nets.binary3(onet.Network).create_belief_propagation_fn()
+    want = o.batch_surprise(u, [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility")],
+                            np.stack([om2[idx], om3[idx]]).astype(np.float32).astype(np.float64), "first_level_binary_surprise")
+    got = a[torch.as_tensor(idx, device="cuda")].double().cpu().numpy()
+    finite = np.isfinite(want)
+    assert np.array_equal(finite, np.isfinite(got))
+    # the grid reaches omega = 0 (saturating, rounding-sensitive: SURVEY §4): hold the well-conditioned part to 1e-4
+    calm = finite & (om2[idx] < -2.0) & (om3[idx] < -2.0)
+    assert calm.sum() > 100
+    assert np.allclose(got[calm], want[calm], rtol=RTOL_SUM)
+    rel = np.abs(got[finite] - want[finite]) / np.abs(want[finite])
+    assert np.median(rel) < 1e-5
+
+
+def test_config5_trajectories_layout(G, datasets):
+    """16-node gHGF with recorded trajectories: every recorded leaf of a batch instance equals the single run."""
+    x = nets.ar1_series(300)
+    g = nets.ghgf16(G.Network)
+    n = 260
+    rng = np.random.default_rng(1)
+    params = {(i, "tonic_volatility"): rng.normal(-4, 0.5, n) for i in range(4, 12)}
+    record = [(i, k) for i in range(16) for k in nets.BELIEFS]
+    res = g.batch(x, params, record=record)
+    for n_i in (0, 129, 259):
+        single = nets.ghgf16(onet.Network)
+        for i in range(4, 12):
+            single.attributes[i]["tonic_volatility"] = float(np.float32(params[(i, "tonic_volatility")][n_i]))
+        single.input_data(x)
+        for i in (4, 9, 12, 15):
+            for k in nets.BELIEFS:
+                got = res.trajectories[(i, k)][n_i].double().cpu().numpy()
+                assert np.allclose(got, single.node_trajectories[i][k], rtol=RTOL_TRAJ, atol=1e-6), (n_i, i, k)

@@ -1,0 +1,148 @@
+"""CPU-side checks: the C-ABI library loads and exports what include/pyhgf_cuda.h declares, the host
+topology compiler derives the reference's schedule, and plan creation validates its input.  No kernel
+is launched here (no GPU in the authoring container)."""
+
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import nets
+from oracle import network as onet
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from pyhgf_b200 import _lib, build
+
+    build.build(verbose=False)
+    return _lib
+
+
+def test_library_exports_every_declared_symbol(lib):
+    header = open(os.path.join(ROOT, "include", "pyhgf_cuda.h")).read()
+    declared = set(re.findall(r"\b(hgf_[a-z_0-9]+)\s*\(", header))
+    assert declared == set(lib.EXPORTS), declared ^ set(lib.EXPORTS)
+    L = lib.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.hgf_abi_version() == 1
+    assert lib.launch_count() == 0
+
+
+def test_struct_layouts_match_the_header(lib):
+    """ctypes mirrors of hgf_topology_t / hgf_call_t: same field order as the header."""
+    header = open(os.path.join(ROOT, "include", "pyhgf_cuda.h")).read()
+
+    def fields(struct_name):
+        end = header.index("} " + struct_name + ";")
+        body = header[header.rindex("typedef struct {", 0, end) + len("typedef struct {"):end]
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        return [re.search(r"(\w+)\s*$", d.strip()).group(1) for d in body.split(";") if d.strip()]
+
+    assert fields("hgf_topology_t") == [f[0] for f in lib.Topology._fields_]
+    assert fields("hgf_call_t") == [f[0] for f in lib.Call._fields_]
+
+
+BUILDERS = [nets.binary3, nets.binary2, nets.continuous2, nets.continuous3, nets.nonlinear, nets.tanh_coupling,
+            nets.volatile2, nets.multi_child, nets.ghgf16]
+
+
+@pytest.mark.parametrize("vu", ["unbounded", "eHGF", "standard"])
+@pytest.mark.parametrize("mf", [False, True])
+@pytest.mark.parametrize("build", BUILDERS, ids=[b.__name__ for b in BUILDERS])
+def test_schedule_and_layout_match_the_oracle(lib, build, vu, mf):
+    from pyhgf_b200.network import Network
+
+    g = build(Network, volatility_updates=vu, mean_field_updates=mf).create_belief_propagation_fn()
+    o = build(onet.Network, volatility_updates=vu, mean_field_updates=mf).create_belief_propagation_fn()
+    assert tuple((i, f.opcode) for i, f in g.update_sequence.prediction_steps) == o.update_sequence[0]
+    assert tuple((i, f.opcode) for i, f in g.update_sequence.update_steps) == o.update_sequence[1]
+    assert g.input_idxs == o.input_idxs
+    assert g.plan.n_slots == o.n_slots
+    for i, e in enumerate(g.edges):
+        assert tuple(e)[:5] == tuple(o.edges[i])[:5]
+        for key, field in [("value_coupling_parents", e.value_parents), ("volatility_coupling_parents", e.volatility_parents),
+                           ("value_coupling_children", e.value_children), ("volatility_coupling_children", e.volatility_children)]:
+            for pos in range(len(field or ())):
+                assert g.plan.slot(i, key, pos) == o.slot(i, key, pos)
+    assert np.array_equal(g._flatten(g.plan).astype(np.float64), o.flatten())
+    assert g.plan.kernel_name  # a variant was selected
+
+
+def test_schedule_counts_of_the_reference(lib):  # tests/test_utils.py:70-92, tests/test_model.py:26-41
+    from pyhgf_b200.network import Network
+
+    n1 = Network().add_nodes(kind="binary-state").add_nodes(value_children=0).create_belief_propagation_fn()
+    assert len(n1.update_sequence.prediction_steps) == 2 and len(n1.update_sequence.update_steps) == 2
+    n2 = (Network(volatility_updates="standard").add_nodes().add_nodes(value_children=0).add_nodes(volatility_children=1)
+          .create_belief_propagation_fn())
+    assert len(n2.update_sequence.prediction_steps) == 3 and len(n2.update_sequence.update_steps) == 4
+    names = [f.__name__ for _, f in nets.binary3(Network).create_belief_propagation_fn().update_sequence.update_steps]
+    assert names == ["binary_state_node_prediction_error", "continuous_node_posterior_update",
+                     "continuous_node_prediction_error", "continuous_node_posterior_update_unbounded"]
+
+
+def test_api_errors_match_the_reference(lib):
+    from pyhgf_b200.network import Network
+
+    with pytest.raises(ValueError, match="Invalid update type"):
+        Network(volatility_updates="fancy")
+    with pytest.raises(ValueError, match="Invalid node type"):
+        Network().add_nodes(kind="quantum-state")
+    with pytest.raises(ValueError, match="not found in the default key"):
+        Network().add_nodes(volatility=3.0)
+    with pytest.raises(ValueError, match="coupling fn and value children do not match"):
+        Network().add_nodes(n_nodes=3).add_nodes(value_children=[0, 1, 2], coupling_fn=(None, None))
+    with pytest.raises(NotImplementedError):
+        Network().add_nodes(kind="ef-state")
+    net = Network().add_nodes().add_nodes(value_children=0)
+    assert net.input_idxs == (0,)
+    assert net.attributes[0]["autoconnection_strength"] == 0.0 and net.attributes[0]["tonic_volatility"] == 0.0
+    net2 = Network().add_nodes().add_nodes(value_children=0)
+    net2.input_idxs = (0,)  # a manual assignment returns before the mutation (network.py:160-176)
+    assert net2.input_idxs == (0,) and net2.attributes[0]["tonic_volatility"] == -4.0
+
+
+def test_plan_create_rejects_bad_topologies(lib):
+    L = lib.lib()
+    topo = lib.Topology()
+    handle = C.c_void_p()
+    assert L.hgf_plan_create(None, C.byref(handle)) != 0
+    topo.n_nodes = 0
+    assert L.hgf_plan_create(C.byref(topo), C.byref(handle)) != 0
+    assert b"n_nodes" in L.hgf_last_error()
+    from pyhgf_b200.network import Network
+    from pyhgf_b200.topology import AdjacencyLists, get_update_sequence
+
+    class Fake:
+        edges = (AdjacencyLists(3, None, None, None, None, (None,)),)
+
+    with pytest.raises(NotImplementedError):
+        get_update_sequence(Fake(), "unbounded")
+    with pytest.raises(NotImplementedError, match="cannot cross the C ABI"):
+        Network().add_nodes().add_nodes(value_children=0, coupling_fn=(lambda x: x**2,)).create_belief_propagation_fn()
+
+
+def test_no_cpu_fallback(lib):
+    """The product fails loudly without a device instead of computing on the host."""
+    import torch
+
+    from pyhgf_b200.network import Network
+
+    if torch.cuda.is_available():
+        pytest.skip("a device is present")
+    with pytest.raises(RuntimeError, match="needs a CUDA device"):
+        nets.binary3(Network).input_data(np.ones(4))
+
+
+def test_product_never_imports_the_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "pyhgf_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text and "liboracle" not in text, f
