@@ -874,6 +874,33 @@ static void store_fields(const Net& net, const State<T>& s, double* slots) {
     for (int k = 0; k < NF; ++k) slots[i * NF + k] = static_cast<double>(pv(s.a[i].f[k]));
 }
 
+template <class B>
+static void batch_grad_impl(const Net& net, long long n_instances, int n_steps, long long group_size, const double* values,
+                            const double* observed, const double* time_steps, const double* slots0, int n_params,
+                            const int* param_slots, const double* params, int response_fn, const double* resp_inputs,
+                            double* surprise_sum, double* grad) {
+  using D = Dual<B, MAXP>;
+  const int n_in = net.n_fed;
+#pragma omp parallel for schedule(static)
+  for (long long n = 0; n < n_instances; ++n) {
+    std::vector<D> slots(net.n_slots);
+    for (int k = 0; k < net.n_slots; ++k) slots[k] = D(static_cast<B>(slots0[k]));
+    for (int q = 0; q < n_params; ++q) {
+      D x(static_cast<B>(params[static_cast<size_t>(q) * n_instances + n]));
+      x.d[q] = B(1);
+      slots[param_slots[q]] = x;
+    }
+    State<D> s; unpack<D>(net, slots.data(), s);
+    long long g = group_size > 0 ? n / group_size : 0;
+    const double* v = values + static_cast<size_t>(g) * n_steps * n_in;
+    const double* o = observed ? observed + static_cast<size_t>(g) * n_steps * n_in : nullptr;
+    const double* r = resp_inputs ? resp_inputs + static_cast<size_t>(g) * n_steps : nullptr;
+    D total = run_surprise_sum<D>(net, s, n_steps, v, o, time_steps, response_fn, r);
+    surprise_sum[n] = static_cast<double>(total.v);
+    for (int q = 0; q < n_params; ++q) grad[static_cast<size_t>(q) * n_instances + n] = static_cast<double>(total.d[q]);
+  }
+}
+
 extern "C" {
 
 void* oracle_net_create(int n_nodes, const int* node_type, const int* vp_ptr, const int* vp_idx, const int* volp_ptr,
@@ -1028,35 +1055,24 @@ int oracle_batch_surprise(void* p, int dtype, long long n_instances, int n_steps
 }
 
 // Batched summed surprise and its gradient wrt the n_params (<= MAXP) batched
-// slots, by forward-mode Dual<double> propagation.  grad [n_params][N].
-int oracle_batch_grad(void* p, long long n_instances, int n_steps, long long group_size, const double* values,
+// slots, by forward-mode Dual propagation (dtype 64: Dual<double>, the reference
+// gradient; dtype 32: Dual<float>, the float32 twin used to check float32
+// kernels like-for-like in rounding-sensitive regimes).  grad [n_params][N].
+int oracle_batch_grad(void* p, int dtype, long long n_instances, int n_steps, long long group_size, const double* values,
                       const double* observed, const double* time_steps, const double* slots0, int n_params,
                       const int* param_slots, const double* params, int response_fn, const double* resp_inputs,
                       double* surprise_sum, double* grad, int n_threads) {
   const Net& net = *static_cast<Net*>(p);
   if (n_params > MAXP) return 1;
-  const int n_in = net.n_fed;
 #ifdef _OPENMP
   if (n_threads > 0) omp_set_num_threads(n_threads);
 #endif
-#pragma omp parallel for schedule(static)
-  for (long long n = 0; n < n_instances; ++n) {
-    std::vector<DualD> slots(net.n_slots);
-    for (int k = 0; k < net.n_slots; ++k) slots[k] = DualD(slots0[k]);
-    for (int q = 0; q < n_params; ++q) {
-      DualD x(params[static_cast<size_t>(q) * n_instances + n]);
-      x.d[q] = 1.0;
-      slots[param_slots[q]] = x;
-    }
-    State<DualD> s; unpack<DualD>(net, slots.data(), s);
-    long long g = group_size > 0 ? n / group_size : 0;
-    const double* v = values + static_cast<size_t>(g) * n_steps * n_in;
-    const double* o = observed ? observed + static_cast<size_t>(g) * n_steps * n_in : nullptr;
-    const double* r = resp_inputs ? resp_inputs + static_cast<size_t>(g) * n_steps : nullptr;
-    DualD total = run_surprise_sum<DualD>(net, s, n_steps, v, o, time_steps, response_fn, r);
-    surprise_sum[n] = total.v;
-    for (int q = 0; q < n_params; ++q) grad[static_cast<size_t>(q) * n_instances + n] = total.d[q];
-  }
+  if (dtype == 32)
+    batch_grad_impl<float>(net, n_instances, n_steps, group_size, values, observed, time_steps, slots0, n_params, param_slots,
+                           params, response_fn, resp_inputs, surprise_sum, grad);
+  else
+    batch_grad_impl<double>(net, n_instances, n_steps, group_size, values, observed, time_steps, slots0, n_params, param_slots,
+                            params, response_fn, resp_inputs, surprise_sum, grad);
   return 0;
 }
 

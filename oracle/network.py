@@ -101,7 +101,7 @@ def lib() -> ctypes.CDLL:
             ctypes.c_int, ip, dp, ctypes.c_int, dp, dp, dp, ctypes.c_int,
         ]
         L.oracle_batch_grad.argtypes = [
-            ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_longlong, dp, dp, dp, dp,
+            ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_longlong, dp, dp, dp, dp,
             ctypes.c_int, ip, dp, ctypes.c_int, dp, dp, dp, ctypes.c_int,
         ]
         L.oracle_binary_surprise.restype = ctypes.c_double
@@ -609,8 +609,9 @@ class Network:
         return (out, last) if return_last else out
 
     def batch_grad(self, values, param_slots, params, response, resp_inputs=None, response_parameters=None,
-                   group_size=0, time_steps=None, observed=None, n_threads=0):
-        """Forward-mode (Dual<double>) gradient oracle: returns (surprise_sum [N], grad [P][N])."""
+                   group_size=0, time_steps=None, observed=None, n_threads=0, dtype=64):
+        """Forward-mode gradient oracle (Dual<double>; dtype=32: the Dual<float> twin): returns
+        (surprise_sum [N], grad [P][N])."""
         if self._handle is None:
             self.create_belief_propagation_fn()
         v = np.asarray(values, dtype=np.float64)
@@ -633,8 +634,12 @@ class Network:
         obs = None if observed is None else np.ascontiguousarray(np.asarray(observed, dtype=np.float64))
         out = np.zeros(n_inst, dtype=np.float64)
         grad = np.zeros((n_params, n_inst), dtype=np.float64)
+        if dtype == 32:
+            v = v.astype(np.float32).astype(np.float64)
+            params = params.astype(np.float32).astype(np.float64)
+            slots0 = slots0.astype(np.float32).astype(np.float64)
         rc = lib().oracle_batch_grad(
-            self._handle, n_inst, n_steps, group_size, _dp(v), _dp(obs), _dp(ts), _dp(slots0), n_params, _ip(ps),
+            self._handle, int(dtype), n_inst, n_steps, group_size, _dp(v), _dp(obs), _dp(ts), _dp(slots0), n_params, _ip(ps),
             _dp(params), RESPONSES[response], _dp(ri), _dp(out), _dp(grad), n_threads,
         )
         assert rc == 0

@@ -23,10 +23,15 @@ OBJ = os.path.join(ROOT, "build", "obj")
 LIB = os.path.join(ROOT, "pyhgf_b200", "lib", "libpyhgf_cuda.so")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+#: "sfu" (default): MUFU-based float32 division/exp/log, FMA contraction; "accurate": IEEE division, libdevice
+#: transcendentals, one rounding per primitive (the validation build) -- see csrc/hgf_math.cuh
+MATH = os.environ.get("HGF_MATH", "sfu")
+if MATH not in ("sfu", "accurate"):
+    raise SystemExit("HGF_MATH must be 'sfu' or 'accurate'")
 COMMON = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
     "-Xcompiler", "-fPIC", "-diag-suppress", "221", "-I", CSRC, "-I", os.path.join(ROOT, "include"),
-]
+] + (["-DHGF_MATH_ACCURATE", "-fmad=false"] if MATH == "accurate" else [])
 
 # interpreter kernels: (tag, scalar type)
 INTERP_SCALARS = [
@@ -59,7 +64,8 @@ def jobs():
                     continue
                 topo, base, ntan = line.split()
                 out.append((os.path.join(CSRC, "hgf_static_inst.cu"), os.path.join(OBJ, f"hgf_static_{topo}_{base}_d{ntan}.o"),
-                            [f"-DHGF_TOPO={topo}", f"-DHGF_BASE={base}", f"-DHGF_NTAN={ntan}"]))
+                            [f"-DHGF_TOPO_HEADER=<generated/topo_{topo}.h>", f"-DHGF_TOPO_TYPE=Topo_{topo}",
+                             f"-DHGF_BASE={base}", f"-DHGF_NTAN={ntan}"] + os.environ.get("HGF_EXTRA_STATIC_FLAGS", "").split()))
     return out
 
 

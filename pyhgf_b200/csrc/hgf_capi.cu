@@ -137,7 +137,7 @@ int hgf_plan_create(const hgf_topology_t* t, hgf_plan_t** out) {
   p.slot_resp = off; off += N_RESP_PARAMS;
   p.n_slots = off;
   plan->variant = select_variant(p);
-  if (!plan->variant->match && p.n_slots > INTERP_SLOTS) {
+  if (!plan->variant->matches && p.n_slots > INTERP_SLOTS) {
     delete plan;
     return fail("hgf_plan_create: network needs %d attribute slots; the interpreter holds %d", off, INTERP_SLOTS);
   }
@@ -176,7 +176,7 @@ static int check_call(const hgf_plan_t* plan, const hgf_call_t* c, bool want_gra
   if (!c->attributes) return fail("attributes is null");
   if (p.n_fed > 0 && c->n_steps > 0 && !c->input_data) return fail("input_data is null");
   if (c->n_params < 0 || c->n_params > MAX_PARAMS) return fail("n_params=%d outside [0, %d]", c->n_params, MAX_PARAMS);
-  if (c->n_params > 0 && (!c->param_slots || !c->params)) return fail("params / param_slots is null");
+  if (c->n_params > 0 && (!c->param_slots || (!c->params && c->n_instances > 0))) return fail("params / param_slots is null");
   if (c->n_records < 0 || c->n_records > MAX_RECORDS) return fail("n_records=%d outside [0, %d]", c->n_records, MAX_RECORDS);
   if (c->trajectories && c->n_records > 0 && !c->record_slots) return fail("record_slots is null");
   if (c->response_fn < RESP_NONE || c->response_fn > RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE) return fail("unknown response_fn %d", c->response_fn);

@@ -1,5 +1,6 @@
 // Kernel variants: the opcode interpreter (any topology) and the generated
-// register-resident specialisations (matched by exact Program equality).
+// register-resident specialisations (selected when every topology query of the
+// lowered Program has the answer the specialisation was generated with).
 #pragma once
 #include <cuda_runtime.h>
 
@@ -12,7 +13,7 @@ using RunFn = cudaError_t (*)(const Program&, const CallLists&, const ScanArgs&,
 
 struct KernelVariant {
   const char* name;
-  const Program* match;  // nullptr: accepts every program
+  bool (*matches)(const Program&);  // nullptr: accepts every program
   RunFn run;
 };
 

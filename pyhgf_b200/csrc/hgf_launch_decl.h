@@ -22,7 +22,7 @@ inline cudaError_t launch_scan(const Program& prog, const CallLists& lists, cons
                                cudaStream_t stream, int* n_launched) {
   if (!want_grad) {
     ++*n_launched;
-    return launch_one<B, Topo, NSLOTS>(prog, lists, args, stream);
+    return launch_one<Dual<B, 0>, Topo, NSLOTS>(prog, lists, args, stream);
   }
   ScanArgs a = args;
   int done = 0;

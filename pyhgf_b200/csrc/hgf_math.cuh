@@ -11,6 +11,18 @@
 //
 // Literal semantics follow the reference's weak-typed Python scalars: a literal
 // adopts the array dtype, so `1e-128` is 0.0f in float32.
+//
+// Math policy (float32 only; float64 always uses IEEE division and libdevice):
+//   default            -- SFU primitives: division = MUFU.RCP x multiply, exp = MUFU.EX2,
+//                         log = MUFU.LG2 (<= 2 ulp each), mul+add contraction allowed.  This is
+//                         what makes the time loop SFU/FP32-pipe bound instead of instruction bound;
+//                         parity with the reference stays inside the stated tolerances
+//                         (tests/test_gpu_parity.py).
+//   -DHGF_MATH_ACCURATE -- IEEE division, libdevice expf/logf/log1pf/powf and -fmad=false
+//                         (one rounding per primitive, the oracle's arithmetic): the validation
+//                         build, `HGF_MATH=accurate python -m pyhgf_b200.build`.
+// Kernels never instantiate a bare float: the plain filter runs on Dual<B, 0>, so every
+// operator below -- in particular operator/ -- is ours.
 #pragma once
 #include <cuda_runtime.h>
 #include <math_constants.h>
@@ -34,7 +46,7 @@ namespace hgf {
 template <class B, int P>
 struct Dual {
   B v;
-  B d[P];
+  B d[P > 0 ? P : 1];  // P = 0: the plain filter (the unused element is never touched and is optimised away)
   HGF_HD Dual() {}
   HGF_HD Dual(B x) : v(x) {  // NOLINT(runtime/explicit)
 #pragma unroll
@@ -45,6 +57,34 @@ struct Dual {
 template <class T> struct scalar_traits { using base = T; static constexpr int n_tangents = 0; };
 template <class B, int P> struct scalar_traits<Dual<B, P>> { using base = B; static constexpr int n_tangents = P; };
 template <class T> using base_t = typename scalar_traits<T>::base;
+
+// The library is compiled with -fmad=false so that primal arithmetic rounds once per operation like the
+// reference's; derivative (tangent) arithmetic has no such contract and uses fused multiply-adds explicitly.
+HGF_HD float b_fma(float a, float b, float c) { return ::fmaf(a, b, c); }
+HGF_HD double b_fma(double a, double b, double c) { return ::fma(a, b, c); }
+
+#if defined(__CUDA_ARCH__) && !defined(HGF_MATH_ACCURATE)
+#define HGF_SFU_MATH 1
+#endif
+// reciprocal and division
+HGF_HD float b_rcp(float x) {
+#ifdef HGF_SFU_MATH
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return 1.0f / x;
+#endif
+}
+HGF_HD double b_rcp(double x) { return 1.0 / x; }
+HGF_HD float b_div(float a, float b) {
+#ifdef HGF_SFU_MATH
+  return a * b_rcp(b);
+#else
+  return a / b;
+#endif
+}
+HGF_HD double b_div(double a, double b) { return a / b; }
 
 HGF_HD float pv(float x) { return x; }
 HGF_HD double pv(double x) { return x; }
@@ -73,14 +113,19 @@ template <class B, int P> HGF_HD Dual<B, P> operator-(const Dual<B, P>& a) {
 template <class B, int P> HGF_HD Dual<B, P> operator*(const Dual<B, P>& a, const Dual<B, P>& b) {
   Dual<B, P> r; r.v = a.v * b.v;
 #pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * b.v + a.v * b.d[i];
+  for (int i = 0; i < P; ++i) r.d[i] = b_fma(a.d[i], b.v, a.v * b.d[i]);
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, const Dual<B, P>& b) {
-  Dual<B, P> r; r.v = a.v / b.v;
-  const B inv = B(1) / b.v;
+  Dual<B, P> r;
+  const B inv = b_rcp(b.v);
+#ifdef HGF_SFU_MATH
+  r.v = a.v * inv;
+#else
+  r.v = b_div(a.v, b.v);
+#endif
 #pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = (a.d[i] - r.v * b.d[i]) * inv;
+  for (int i = 0; i < P; ++i) r.d[i] = b_fma(-r.v, b.d[i], a.d[i]) * inv;
   return r;
 }
 // scalar (tangent-free) operands
@@ -96,29 +141,49 @@ template <class B, int P> HGF_HD Dual<B, P> operator*(const Dual<B, P>& a, B b) 
 }
 template <class B, int P> HGF_HD Dual<B, P> operator*(B a, const Dual<B, P>& b) { return b * a; }
 template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, B b) {
-  Dual<B, P> r; r.v = a.v / b;
-  const B inv = B(1) / b;
+  Dual<B, P> r; r.v = b_div(a.v, b);
+  if constexpr (P > 0) {
+    const B inv = b_rcp(b);
 #pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
+    for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
+  }
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator/(B a, const Dual<B, P>& b) {
-  Dual<B, P> r; r.v = a / b.v;
-  const B c = -r.v / b.v;
+  Dual<B, P> r;
+  const B inv = b_rcp(b.v);
+#ifdef HGF_SFU_MATH
+  r.v = a * inv;
+#else
+  r.v = b_div(a, b.v);
+#endif
+  if constexpr (P > 0) {
+    const B c = -r.v * inv;
 #pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = c * b.d[i];
+    for (int i = 0; i < P; ++i) r.d[i] = c * b.d[i];
+  }
   return r;
 }
 
 // ----------------------------------------------------------------------------
-// Elementary functions (accurate libdevice versions: the parity build never
-// uses the --use_fast_math intrinsics)
+// Elementary functions (float32: SFU primitives by default, libdevice with
+// -DHGF_MATH_ACCURATE; see the math policy at the top of this file)
 // ----------------------------------------------------------------------------
+#ifdef HGF_SFU_MATH
+HGF_D float sfu_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+HGF_D float sfu_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+HGF_D float b_exp(float x) { return sfu_ex2(x * 1.4426950408889634f); }
+HGF_D float b_log(float x) { return sfu_lg2(x) * 0.6931471805599453f; }
+HGF_D float b_log1p(float x) { return b_log(1.0f + x); }
+HGF_D float b_pow(float x, float y) { return sfu_ex2(y * sfu_lg2(x)); }
+#else
 HGF_D float b_exp(float x) { return ::expf(x); }
-HGF_D double b_exp(double x) { return ::exp(x); }
 HGF_D float b_log(float x) { return ::logf(x); }
-HGF_D double b_log(double x) { return ::log(x); }
 HGF_D float b_log1p(float x) { return ::log1pf(x); }
+HGF_D float b_pow(float x, float y) { return ::powf(x, y); }
+#endif
+HGF_D double b_exp(double x) { return ::exp(x); }
+HGF_D double b_log(double x) { return ::log(x); }
 HGF_D double b_log1p(double x) { return ::log1p(x); }
 HGF_D float b_sin(float x) { return ::sinf(x); }
 HGF_D double b_sin(double x) { return ::sin(x); }
@@ -130,7 +195,6 @@ HGF_D float b_erf(float x) { return ::erff(x); }
 HGF_D double b_erf(double x) { return ::erf(x); }
 HGF_D float b_abs(float x) { return ::fabsf(x); }
 HGF_D double b_abs(double x) { return ::fabs(x); }
-HGF_D float b_pow(float x, float y) { return ::powf(x, y); }
 HGF_D double b_pow(double x, double y) { return ::pow(x, y); }
 HGF_D bool b_isnan(float x) { return x != x; }
 HGF_D bool b_isnan(double x) { return x != x; }
@@ -170,9 +234,11 @@ template <class B, int P> HGF_D Dual<B, P> x_exp(const Dual<B, P>& a) {
 }
 template <class B, int P> HGF_D Dual<B, P> x_log(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_log(a.v);
-  const B inv = B(1) / a.v;
+  if constexpr (P > 0) {
+    const B inv = b_rcp(a.v);
 #pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
+    for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
+  }
   return r;
 }
 template <class B, int P> HGF_D Dual<B, P> x_sin(const Dual<B, P>& a) {
@@ -203,13 +269,19 @@ template <class B, int P> HGF_D Dual<B, P> x_erf(const Dual<B, P>& a) {
 template <class B, int P> HGF_D Dual<B, P> x_pow(const Dual<B, P>& a, const Dual<B, P>& b) {
   // jnp.power JVP: y x^(y-1) dx + log(x) x^y dy
   Dual<B, P> r; r.v = b_pow(a.v, b.v);
-  const B da = b.v * b_pow(a.v, b.v - B(1));
-  const B db = b_log(a.v) * r.v;
+  if constexpr (P > 0) {
+#ifdef HGF_SFU_MATH
+    const B da = b.v * r.v * b_rcp(a.v);
+#else
+    const B da = b.v * b_pow(a.v, b.v - B(1));
+#endif
+    const B db = b_log(a.v) * r.v;
 #pragma unroll
-  for (int i = 0; i < P; ++i) {
-    B t = da * a.d[i];
-    if (b.d[i] != B(0)) t += db * b.d[i];
-    r.d[i] = t;
+    for (int i = 0; i < P; ++i) {
+      B t = da * a.d[i];
+      if (b.d[i] != B(0)) t = b_fma(db, b.d[i], t);
+      r.d[i] = t;
+    }
   }
   return r;
 }
@@ -251,9 +323,11 @@ HGF_D double x_logaddexp(double a, double b) { return b_logaddexp<double>(a, b);
 template <class B, int P> HGF_D Dual<B, P> x_logaddexp(const Dual<B, P>& a, const Dual<B, P>& b) {
   // JVP of jnp.logaddexp: t1 * exp(x1 - out) + t2 * exp(x2 - out)
   Dual<B, P> r; r.v = b_logaddexp<B>(a.v, b.v);
-  const B wa = b_exp(a.v - r.v), wb = b_exp(b.v - r.v);
+  if constexpr (P > 0) {
+    const B wa = b_exp(a.v - r.v), wb = b_exp(b.v - r.v);
 #pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * wa + b.d[i] * wb;
+    for (int i = 0; i < P; ++i) r.d[i] = b_fma(a.d[i], wa, b.d[i] * wb);
+  }
   return r;
 }
 
@@ -266,7 +340,7 @@ template <class B> HGF_D B b_lambert_w0(B z) {
     const B f = w * ew - z;
     const B f1 = (w + B(1)) * ew;
     const B f2 = (w + B(2)) * ew;
-    w = w - (B(2) * f * f1) / (B(2) * (f1 * f1) - f * f2);
+    w = w - b_div(B(2) * f * f1, B(2) * (f1 * f1) - f * f2);
   }
   return w;
 }
@@ -275,9 +349,11 @@ HGF_D double x_lambert_w0(double z) { return b_lambert_w0<double>(z); }
 template <class B, int P> HGF_D Dual<B, P> x_lambert_w0(const Dual<B, P>& z) {
   // custom JVP, pyhgf/math.py:491-498: z_dot / (exp(w) (1 + w))
   Dual<B, P> r; r.v = b_lambert_w0<B>(z.v);
-  const B inv = B(1) / (b_exp(r.v) * (B(1) + r.v));
+  if constexpr (P > 0) {
+    const B inv = b_rcp(b_exp(r.v) * (B(1) + r.v));
 #pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = z.d[i] * inv;
+    for (int i = 0; i < P; ++i) r.d[i] = z.d[i] * inv;
+  }
   return r;
 }
 

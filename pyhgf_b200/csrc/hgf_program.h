@@ -105,6 +105,10 @@ struct ScanArgs {
   double out_scale;
   int response_fn;
   int tangent_offset;  // this pass differentiates params [tangent_offset, tangent_offset + P)
+  // register-resident specialisations: which belief leaves (mean, expected_mean, precision,
+  // expected_precision per node, + the *_vol twins of volatile nodes, in slot order) are recorded;
+  // leaf r is stored in trajectory row popcount(mask below r)
+  uint32_t rec_mask[4];
 };
 
 }  // namespace hgf

@@ -93,15 +93,17 @@ HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArg
     }
     if (traj && active) {
       if constexpr (Topo::is_static) {
-        // static record set: the four belief leaves of every node (+ the volatility-level twins)
-        int r = 0;
+        // static leaf set (see ScanArgs::rec_mask): warp-uniform predicates, coalesced stores
+        int leaf = 0, row = 0;
 #pragma unroll
         for (int node = 0; node < a.n_nodes(); ++node) {
 #pragma unroll
-          for (int f = 0; f < 4; ++f) traj[(static_cast<long long>(r++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
+          for (int f = 0; f < 4; ++f, ++leaf)
+            if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) traj[(static_cast<long long>(row++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
           if (a.node_type(node) == NODE_VOLATILE) {
 #pragma unroll
-            for (int f = F_MEAN_VOL; f < F_MEAN_VOL + 4; ++f) traj[(static_cast<long long>(r++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
+            for (int f = F_MEAN_VOL; f < F_MEAN_VOL + 4; ++f, ++leaf)
+              if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) traj[(static_cast<long long>(row++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
           }
         }
       } else {

@@ -6,7 +6,7 @@ namespace hgf {
 
 const KernelVariant* select_variant(const Program& prog) {
   for (const KernelVariant* const* v = static_variants(); *v; ++v)
-    if ((*v)->match && std::memcmp((*v)->match, &prog, sizeof(Program)) == 0) return *v;
+    if ((*v)->matches && (*v)->matches(prog)) return *v;
   return &kInterpreterVariant;
 }
 

@@ -1,5 +1,30 @@
-#include "hgf_dispatch.h"
+// Table of the generated register-resident specialisations (pyhgf_b200/codegen.py
+// writes generated/topo_*.h and generated/static_table.inc).  Kernel bodies are
+// instantiated in hgf_static_inst.cu, one (topology, scalar type) per translation unit.
+#include "hgf_static_run.h"
+
+#if __has_include(<generated/static_includes.inc>)
+#include <generated/static_includes.inc>
+#endif
+
 namespace hgf {
-static const KernelVariant* const kNone[] = {nullptr};
-const KernelVariant* const* static_variants() { return kNone; }
-}
+
+#define HGF_STATIC_TOPO(name, mask32, mask64)                                                        \
+  static const KernelVariant kVariant_##name = {"static:" #name, topo_matches<Topo_##name>,          \
+                                                run_static_any<Topo_##name, mask32, mask64>};
+#if __has_include(<generated/static_table.inc>)
+#include <generated/static_table.inc>
+#endif
+#undef HGF_STATIC_TOPO
+
+static const KernelVariant* const kStatic[] = {
+#define HGF_STATIC_TOPO(name, mask32, mask64) &kVariant_##name,
+#if __has_include(<generated/static_table.inc>)
+#include <generated/static_table.inc>
+#endif
+#undef HGF_STATIC_TOPO
+    nullptr};
+
+const KernelVariant* const* static_variants() { return kStatic; }
+
+}  // namespace hgf

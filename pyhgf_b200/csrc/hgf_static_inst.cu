@@ -1,0 +1,11 @@
+// One register-resident kernel per translation unit: compile with
+//   -DHGF_TOPO_HEADER=<generated/topo_NAME.h> -DHGF_TOPO_TYPE=Topo_NAME
+//   -DHGF_BASE=float|double -DHGF_NTAN=<tangent directions, 0 = plain filter>.
+#include "hgf_launch.cuh"
+#include HGF_TOPO_HEADER
+
+namespace hgf {
+using Scalar = Dual<HGF_BASE, HGF_NTAN>;  // 0 tangents: the plain filter
+template cudaError_t launch_one<Scalar, HGF_TOPO_TYPE, HGF_TOPO_TYPE::kSlots>(const Program&, const CallLists&, const ScanArgs&,
+                                                                             cudaStream_t);
+}
