@@ -62,10 +62,10 @@ def jobs():
                 line = line.strip()
                 if not line or line.startswith("#"):
                     continue
-                topo, base, ntan = line.split()
-                out.append((os.path.join(CSRC, "hgf_static_inst.cu"), os.path.join(OBJ, f"hgf_static_{topo}_{base}_d{ntan}.o"),
+                topo, base, ntan, nresp = line.split()
+                out.append((os.path.join(CSRC, "hgf_static_inst.cu"), os.path.join(OBJ, f"hgf_static_{topo}_{base}_d{ntan}r{nresp}.o"),
                             [f"-DHGF_TOPO_HEADER=<generated/topo_{topo}.h>", f"-DHGF_TOPO_TYPE=Topo_{topo}",
-                             f"-DHGF_BASE={base}", f"-DHGF_NTAN={ntan}"] + os.environ.get("HGF_EXTRA_STATIC_FLAGS", "").split()))
+                             f"-DHGF_BASE={base}", f"-DHGF_NTAN={ntan}", f"-DHGF_NRESP={nresp}"] + os.environ.get("HGF_EXTRA_STATIC_FLAGS", "").split()))
     return out
 
 

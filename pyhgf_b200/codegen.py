@@ -86,13 +86,15 @@ def _ghgf16():
     return g
 
 
-#: name -> (graph factory, volatility_updates, mean_field, f32 tangent widths, f64 tangent widths)
+#: name -> (graph factory, volatility_updates, mean_field, float32 kernels, float64 kernels); a kernel is
+#: (PF, PR): PF filter tangent directions, PR response-parameter-only tangent directions (0 or 1)
+_ALL = tuple((pf, pr) for pr in (0, 1) for pf in range(5))
 TOPOLOGIES = {
-    "binary2": (lambda: _binary(2), "unbounded", False, (0, 1, 2, 3, 4), (0,)),
-    "binary3": (lambda: _binary(3), "unbounded", False, (0, 1, 2, 3, 4), (0, 4)),
-    "continuous2": (lambda: _continuous(2), "unbounded", False, (0, 3), (0,)),
-    "continuous3": (lambda: _continuous(3), "unbounded", False, (0, 3, 4), (0,)),
-    "ghgf16": (_ghgf16, "unbounded", False, (0,), ()),
+    "binary2": (lambda: _binary(2), "unbounded", False, _ALL, ((0, 0),)),
+    "binary3": (lambda: _binary(3), "unbounded", False, _ALL, ((0, 0), (4, 0))),
+    "continuous2": (lambda: _continuous(2), "unbounded", False, ((0, 0), (3, 0)), ((0, 0),)),
+    "continuous3": (lambda: _continuous(3), "unbounded", False, ((0, 0), (3, 0), (4, 0)), ((0, 0),)),
+    "ghgf16": (_ghgf16, "unbounded", False, ((0, 0),), ()),
 }
 
 
@@ -197,17 +199,17 @@ def _write_if_changed(path, text):
 
 def main():
     os.makedirs(GEN, exist_ok=True)
-    includes, table, manifest = [], [], ["# topology base n_tangents  (one translation unit each; written by codegen.py)\n"]
+    includes, table, manifest = [], [], ["# topology base PF PR  (one translation unit each; written by codegen.py)\n"]
     for name, spec in TOPOLOGIES.items():
         _write_if_changed(os.path.join(GEN, f"topo_{name}.h"), generate_topology(name, spec))
         includes.append(f"#include <generated/topo_{name}.h>\n")
-        m32 = sum(1 << k for k in spec[3])
-        m64 = sum(1 << k for k in spec[4])
+        m32 = sum(1 << (pf + 5 * pr) for pf, pr in spec[3])
+        m64 = sum(1 << (pf + 5 * pr) for pf, pr in spec[4])
         table.append(f"HGF_STATIC_TOPO({name}, {m32}u, {m64}u)\n")
-        for k in spec[3]:
-            manifest.append(f"{name} float {k}\n")
-        for k in spec[4]:
-            manifest.append(f"{name} double {k}\n")
+        for pf, pr in spec[3]:
+            manifest.append(f"{name} float {pf} {pr}\n")
+        for pf, pr in spec[4]:
+            manifest.append(f"{name} double {pf} {pr}\n")
     _write_if_changed(os.path.join(GEN, "static_includes.inc"), "".join(includes))
     _write_if_changed(os.path.join(GEN, "static_table.inc"), "".join(table))
     _write_if_changed(os.path.join(GEN, "instances.txt"), "".join(manifest))

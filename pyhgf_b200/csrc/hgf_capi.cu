@@ -189,10 +189,19 @@ static int check_call(const hgf_plan_t* plan, const hgf_call_t* c, bool want_gra
   if (!want_grad && c->gradient) return fail("hgf_filter: gradient must be null (use hgf_logp_grad)");
   std::memset(&lists, 0, sizeof lists);
   lists.n_params = c->n_params;
-  for (int i = 0; i < c->n_params; ++i) {
-    if (c->param_slots[i] < 0 || c->param_slots[i] >= p.n_slots) return fail("param slot %d out of range", c->param_slots[i]);
-    lists.param_slot[i] = static_cast<uint16_t>(c->param_slots[i]);
-  }
+  // launch order: parameters of the filter first, response-function parameters last (their tangents
+  // never enter the filter: hgf_program.h); param_row keeps each one's row in the caller's arrays
+  int k = 0;
+  for (int pass = 0; pass < 2; ++pass)
+    for (int i = 0; i < c->n_params; ++i) {
+      if (c->param_slots[i] < 0 || c->param_slots[i] >= p.n_slots) return fail("param slot %d out of range", c->param_slots[i]);
+      const bool is_response = c->param_slots[i] >= p.slot_resp;
+      if (is_response != (pass == 1)) continue;
+      lists.param_slot[k] = static_cast<uint16_t>(c->param_slots[i]);
+      lists.param_row[k] = static_cast<uint16_t>(i);
+      ++k;
+      if (pass == 0) lists.n_filter = k;
+    }
   lists.n_rec = c->trajectories ? c->n_records : 0;
   for (int i = 0; i < lists.n_rec; ++i) {
     if (c->record_slots[i] < 0 || c->record_slots[i] >= p.n_slots) return fail("record slot %d out of range", c->record_slots[i]);

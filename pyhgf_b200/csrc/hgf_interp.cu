@@ -10,8 +10,9 @@ namespace hgf {
 static cudaError_t run_interpreter(const Program& prog, const CallLists& lists, const ScanArgs& args, int dtype, bool want_grad,
                                    cudaStream_t stream, int* n_launched) {
   if (prog.n_slots > INTERP_SLOTS) return cudaErrorInvalidValue;  // rejected earlier by hgf_plan_create
-  if (dtype == 32) return launch_scan<float, RuntimeTopo, INTERP_SLOTS, true>(prog, lists, args, want_grad, stream, n_launched);
-  return launch_scan<double, RuntimeTopo, INTERP_SLOTS, false>(prog, lists, args, want_grad, stream, n_launched);
+  // instantiated in hgf_interp_inst.cu: float PF = 0..4, double PF = 0 and 4; no response-only tangents
+  if (dtype == 32) return launch_scan<float, RuntimeTopo, INTERP_SLOTS, 0x1fu>(prog, lists, args, want_grad, stream, n_launched);
+  return launch_scan<double, RuntimeTopo, INTERP_SLOTS, 0x11u>(prog, lists, args, want_grad, stream, n_launched);
 }
 
 const KernelVariant kInterpreterVariant = {"interpreter", nullptr, run_interpreter};

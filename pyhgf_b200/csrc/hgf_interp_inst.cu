@@ -4,5 +4,5 @@
 
 namespace hgf {
 using Scalar = Dual<HGF_BASE, HGF_NTAN>;  // 0 tangents: the plain filter
-template cudaError_t launch_one<Scalar, RuntimeTopo, INTERP_SLOTS>(const Program&, const CallLists&, const ScanArgs&, cudaStream_t);
+template cudaError_t launch_one<Scalar, RuntimeTopo, INTERP_SLOTS, 0>(const Program&, const CallLists&, const ScanArgs&, cudaStream_t);
 }

@@ -1,5 +1,5 @@
 // Declarations shared by the dispatching translation units (which never see
-// kernel bodies) and the instantiating ones.
+// kernel bodies) and the instantiating ones, and the pass logic of the gradient.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -10,32 +10,64 @@ namespace hgf {
 
 struct RuntimeTopo;
 
-template <class T, class Topo, int NSLOTS>
+// One kernel launch: the filter runs on T = Dual<B, PF>; PR extra tangent directions live only
+// inside the response function.  Defined (and explicitly instantiated) in hgf_launch.cuh users.
+template <class T, class Topo, int NSLOTS, int PR>
 cudaError_t launch_one(const Program& prog, const CallLists& lists, const ScanArgs& args, cudaStream_t stream);
 
-// Forward filter: one launch.  Gradient: forward-mode passes of up to four
-// tangent directions each; the first pass also produces the non-gradient
-// outputs.  NARROW = false restricts the passes to width 4 (fewer kernels to
-// build; used for float64).
-template <class B, class Topo, int NSLOTS, bool NARROW>
-inline cudaError_t launch_scan(const Program& prog, const CallLists& lists, const ScanArgs& args, bool want_grad,
-                               cudaStream_t stream, int* n_launched) {
-  if (!want_grad) {
-    ++*n_launched;
-    return launch_one<Dual<B, 0>, Topo, NSLOTS>(prog, lists, args, stream);
+// Which (PF, PR) kernels of a (topology, base type) were instantiated: bit PF + 5 * PR.
+constexpr unsigned variant_bit(int pf, int pr) { return 1u << (pf + 5 * pr); }
+
+template <class B, class Topo, int NSLOTS, unsigned MASK>
+cudaError_t launch_variant(int pf, int pr, const Program& prog, const CallLists& lists, const ScanArgs& args, cudaStream_t stream) {
+#define HGF_TRY(PF_, PR_)                                                                  \
+  if constexpr ((MASK & variant_bit(PF_, PR_)) != 0) {                                     \
+    if (pf == PF_ && pr == PR_) return launch_one<Dual<B, PF_>, Topo, NSLOTS, PR_>(prog, lists, args, stream); \
   }
-  ScanArgs a = args;
-  int done = 0;
-  while (done < lists.n_params) {
-    const int rem = lists.n_params - done;
-    a.tangent_offset = done;
-    cudaError_t err;
-    if (rem >= 4 || !NARROW) { err = launch_one<Dual<B, 4>, Topo, NSLOTS>(prog, lists, a, stream); done += 4; }
-    else if (rem == 3) { err = launch_one<Dual<B, NARROW ? 3 : 4>, Topo, NSLOTS>(prog, lists, a, stream); done += 3; }
-    else if (rem == 2) { err = launch_one<Dual<B, NARROW ? 2 : 4>, Topo, NSLOTS>(prog, lists, a, stream); done += 2; }
-    else { err = launch_one<Dual<B, NARROW ? 1 : 4>, Topo, NSLOTS>(prog, lists, a, stream); done += 1; }
+  HGF_TRY(0, 0) HGF_TRY(1, 0) HGF_TRY(2, 0) HGF_TRY(3, 0) HGF_TRY(4, 0)
+  HGF_TRY(0, 1) HGF_TRY(1, 1) HGF_TRY(2, 1) HGF_TRY(3, 1) HGF_TRY(4, 1)
+#undef HGF_TRY
+  return cudaErrorInvalidValue;
+}
+
+// Forward filter: one launch.  Gradient: forward-mode passes of up to four filter-parameter
+// tangents (+ one response-parameter tangent) each; the first pass also produces the
+// non-gradient outputs.  Returns cudaErrorNotSupported if MASK lacks the kernels needed.
+template <class B, class Topo, int NSLOTS, unsigned MASK>
+cudaError_t launch_scan(const Program& prog, const CallLists& lists_in, const ScanArgs& args_in, bool want_grad,
+                        cudaStream_t stream, int* n_launched) {
+  CallLists lists = lists_in;
+  ScanArgs a = args_in;
+  a.tangent_offset = 0;
+  a.resp_index = -1;
+  constexpr bool kHasResp = (MASK >> 5) != 0;
+  if (!kHasResp || !want_grad) lists.n_filter = lists.n_params;  // response parameters ride along as filter parameters
+  if (!want_grad) {
+    if ((MASK & 1u) == 0) return cudaErrorNotSupported;
+    ++*n_launched;
+    return launch_variant<B, Topo, NSLOTS, MASK>(0, 0, prog, lists, a, stream);
+  }
+  const int F = lists.n_filter, R = lists.n_params - lists.n_filter;
+  int done_f = 0, done_r = 0;
+  while (done_f < F || done_r < R) {
+    const int remf = F - done_f;
+    int pr = done_r < R ? 1 : 0, pf = -1;
+    for (int attempt = 0; attempt < 2 && pf < 0; ++attempt) {
+      for (int k = 4; k >= 0; --k)  // widest kernel that is not wider than what is left ...
+        if ((MASK & variant_bit(k, pr)) && k <= remf && (k > 0 || pr > 0)) { pf = k; break; }
+      if (pf < 0)
+        for (int k = 1; k <= 4; ++k)  // ... else the narrowest one that covers it
+          if ((MASK & variant_bit(k, pr)) && k >= remf) { pf = k; break; }
+      if (pf < 0 && pr == 1 && remf > 0) pr = 0; else break;
+    }
+    if (pf < 0) return cudaErrorNotSupported;
+    a.tangent_offset = done_f;
+    a.resp_index = pr ? F + done_r : -1;
+    const cudaError_t err = launch_variant<B, Topo, NSLOTS, MASK>(pf, pr, prog, lists, a, stream);
     ++*n_launched;
     if (err != cudaSuccess) return err;
+    done_f += pf < remf ? pf : remf;
+    done_r += pr;
     // later passes only add gradient columns
     a.trajectories = nullptr; a.last_attributes = nullptr; a.surprise_sum = nullptr; a.surprise_pointwise = nullptr; a.reduced = nullptr;
   }

@@ -53,6 +53,13 @@ struct RuntimeTopo {
 
 #define HGF_S(node, field) s[(node) * NF + (field)]
 
+// The time step of the current slice and its logarithm (the "unbounded" update works in log
+// space); computed once per slice by the scan -- and folded to (1, 0) when the call has no
+// time_steps vector.
+template <class T> struct Step {
+  T dt, log_dt;
+};
+
 // ---------------------------------------------------------------------------
 // coupling functions g, g', g''.  The reference differentiates the user's
 // callable with jax.grad (prediction/continuous.py:252,
@@ -121,7 +128,7 @@ template <class T, class A> HGF_D void predict_binary(const A& a, T* s, int node
 
 // predict_mean, prediction/continuous.py:11-103 (volatile twin: volatile.py:51-108,
 // which has no tonic drift).
-template <class T, class A> HGF_D T predicted_mean(const A& a, const T* s, const T& dt, int node, bool is_volatile) {
+template <class T, class A> HGF_D T predicted_mean(const A& a, const T* s, const Step<T>& st, int node, bool is_volatile) {
   using B = base_t<T>;
   T drift = is_volatile ? T(B(0)) : HGF_S(node, F_TONIC_DRIFT);
 #pragma unroll (A::kUnroll)
@@ -131,11 +138,11 @@ template <class T, class A> HGF_D T predicted_mean(const A& a, const T* s, const
     const T mu_par = HGF_S(par, F_EXPECTED_MEAN);
     drift = drift + s[a.slot_cvp(node, k)] * (fn == CF_LINEAR ? mu_par : cf_value(fn, mu_par));
   }
-  return HGF_S(node, F_AUTOCONNECTION_STRENGTH) * HGF_S(node, F_MEAN) + dt * drift;
+  return HGF_S(node, F_AUTOCONNECTION_STRENGTH) * HGF_S(node, F_MEAN) + st.dt * drift;
 }
 
 // Laplace term of the value parents, prediction/continuous.py:240-257.
-template <class T, class A> HGF_D T value_parent_variance(const A& a, const T* s, const T& dt, int node) {
+template <class T, class A> HGF_D T value_parent_variance(const A& a, const T* s, const Step<T>& st, int node) {
   using B = base_t<T>;
   T var = T(B(0));
 #pragma unroll (A::kUnroll)
@@ -143,7 +150,7 @@ template <class T, class A> HGF_D T value_parent_variance(const A& a, const T* s
     const int par = a.vp(node, k);
     const int fn = a.vp_fn(node, k);
     const T slope = (fn == CF_LINEAR) ? T(B(1)) : cf_prime(fn, HGF_S(par, F_EXPECTED_MEAN));
-    const T c = dt * s[a.slot_cvp(node, k)] * slope;
+    const T c = st.dt * s[a.slot_cvp(node, k)] * slope;
     var = var + (c * c) / HGF_S(par, F_EXPECTED_PRECISION);
   }
   return var;
@@ -157,11 +164,11 @@ template <class T> HGF_D T nan_unless_positive(const T& x) {
 
 // continuous_node_prediction, prediction/continuous.py:282-366 (relaxed scheme
 // :106-279) and its mean-field variant :369-512.
-template <class T, class A> HGF_D void predict_continuous(const A& a, T* s, const T& dt, int node, bool mean_field) {
+template <class T, class A> HGF_D void predict_continuous(const A& a, T* s, const Step<T>& st, int node, bool mean_field) {
   using B = base_t<T>;
   const T variance = B(1) / HGF_S(node, F_PRECISION);
   HGF_S(node, F_CURRENT_VARIANCE) = variance;
-  const T mu_hat = predicted_mean(a, s, dt, node, false);
+  const T mu_hat = predicted_mean(a, s, st, node, false);
   T log_vol = HGF_S(node, F_TONIC_VOLATILITY);
 #pragma unroll (A::kUnroll)
   for (int k = 0; k < a.n_volp(node); ++k) {
@@ -170,13 +177,13 @@ template <class T, class A> HGF_D void predict_continuous(const A& a, T* s, cons
     log_vol = log_vol + kappa * HGF_S(par, F_EXPECTED_MEAN);
     if (!mean_field) log_vol = log_vol + (kappa * kappa) / (B(2) * HGF_S(par, F_EXPECTED_PRECISION));  // MGF term
   }
-  const T omega = nan_unless_positive(dt * x_exp(log_vol));
+  const T omega = nan_unless_positive(st.dt * x_exp(log_vol));
   T pi_cond, pi_marg;
   if (mean_field) {
     pi_cond = B(1) / (variance + omega);
     pi_marg = pi_cond;
   } else {
-    const T var_parents = value_parent_variance(a, s, dt, node);
+    const T var_parents = value_parent_variance(a, s, st, node);
     pi_cond = B(1) / (variance + omega);
     pi_marg = B(1) / (variance + omega + var_parents);
   }
@@ -193,28 +200,28 @@ template <class T, class A> HGF_D void predict_continuous(const A& a, T* s, cons
 
 // volatile_node_prediction, prediction/volatile.py:230-309 (helpers :9-227),
 // mean-field :312-429: implicit volatility level first, then the value level.
-template <class T, class A> HGF_D void predict_volatile(const A& a, T* s, const T& dt, int node, bool mean_field) {
+template <class T, class A> HGF_D void predict_volatile(const A& a, T* s, const Step<T>& st, int node, bool mean_field) {
   using B = base_t<T>;
   const T variance = B(1) / HGF_S(node, F_PRECISION);
   HGF_S(node, F_CURRENT_VARIANCE) = variance;
-  const T omega_vol = nan_unless_positive(dt * x_exp(HGF_S(node, F_TONIC_VOLATILITY_VOL)));
+  const T omega_vol = nan_unless_positive(st.dt * x_exp(HGF_S(node, F_TONIC_VOLATILITY_VOL)));
   const T pi_hat_vol = B(1) / (B(1) / HGF_S(node, F_PRECISION_VOL) + omega_vol);
   const T mu_hat_vol = HGF_S(node, F_MEAN_VOL);
   HGF_S(node, F_EXPECTED_MEAN_VOL) = mu_hat_vol;
   HGF_S(node, F_EXPECTED_PRECISION_VOL) = pi_hat_vol;
   HGF_S(node, F_EFFECTIVE_PRECISION_VOL) = omega_vol * pi_hat_vol;
   const T log_vol = mean_field ? mu_hat_vol : mu_hat_vol + B(1) / (B(2) * pi_hat_vol);
-  const T omega = nan_unless_positive(dt * x_exp(log_vol));
+  const T omega = nan_unless_positive(st.dt * x_exp(log_vol));
   T pi_cond, pi_marg;
   if (mean_field) {
     pi_cond = B(1) / (variance + omega);
     pi_marg = pi_cond;
   } else {
-    const T var_parents = value_parent_variance(a, s, dt, node);
+    const T var_parents = value_parent_variance(a, s, st, node);
     pi_cond = B(1) / (variance + omega);
     pi_marg = B(1) / (variance + omega + var_parents);
   }
-  HGF_S(node, F_EXPECTED_MEAN) = predicted_mean(a, s, dt, node, true);
+  HGF_S(node, F_EXPECTED_MEAN) = predicted_mean(a, s, st, node, true);
   if (a.n_vc(node) == 0 && a.n_volc(node) == 0 && a.n_volp(node) == 0) {  // :288-301
     HGF_S(node, F_EXPECTED_PRECISION) = HGF_S(node, F_PRECISION);
     HGF_S(node, F_CONDITIONAL_EXPECTED_PRECISION) = HGF_S(node, F_PRECISION);
@@ -287,10 +294,10 @@ template <class T, class A> HGF_D T child_gain_precision(const A& a, const T* s,
 
 // eHGF re-predicted volatility increment,
 // posterior_update_precision_continuous_node.py:564-624.
-template <class T> HGF_D T ehgf_increment(const T* s, const T& dt, int node, int child, const T& kappa) {
+template <class T> HGF_D T ehgf_increment(const T* s, const Step<T>& st, int node, int child, const T& kappa) {
   using B = base_t<T>;
   const T prev_var = HGF_S(child, F_CURRENT_VARIANCE);
-  const T omega = dt * x_exp(kappa * HGF_S(node, F_MEAN) + HGF_S(child, F_TONIC_VOLATILITY));
+  const T omega = st.dt * x_exp(kappa * HGF_S(node, F_MEAN) + HGF_S(child, F_TONIC_VOLATILITY));
   const T pi_hat = B(1) / (prev_var + omega);
   const T gamma = omega * pi_hat;
   const T weight = (omega - prev_var) * pi_hat;
@@ -304,7 +311,7 @@ template <class T> HGF_D T ehgf_increment(const T* s, const T& dt, int node, int
 // posterior_update_precision_continuous_node.py:208-365, 425-561, 627-750;
 // the unobserved branch of its lax.cond is precision_update_missing_values :368-422.
 template <class T, class A>
-HGF_D T posterior_precision(const A& a, const T* s, const T& dt, int node, bool mean_field, bool ehgf) {
+HGF_D T posterior_precision(const A& a, const T* s, const Step<T>& st, int node, bool mean_field, bool ehgf) {
   using B = base_t<T>;
   bool any_observed = false;
 #pragma unroll (A::kUnroll)
@@ -315,7 +322,7 @@ HGF_D T posterior_precision(const A& a, const T* s, const T& dt, int node, bool 
     T log_vol = HGF_S(node, F_TONIC_VOLATILITY);
 #pragma unroll (A::kUnroll)
     for (int k = 0; k < a.n_volp(node); ++k) log_vol = log_vol + s[a.slot_cvolp(node, k)] * HGF_S(a.volp(node, k), F_MEAN);
-    return B(1) / (B(1) / HGF_S(node, F_PRECISION) + dt * x_exp(log_vol));
+    return B(1) / (B(1) / HGF_S(node, F_PRECISION) + st.dt * x_exp(log_vol));
   }
   T from_values = T(B(0));
 #pragma unroll (A::kUnroll)
@@ -338,7 +345,7 @@ HGF_D T posterior_precision(const A& a, const T* s, const T& dt, int node, bool 
     const int child = a.volc(node, k);
     const T kappa = s[a.slot_cvolc(node, k)];
     if (ehgf) {
-      from_volatility = from_volatility + ehgf_increment(s, dt, node, child, kappa);
+      from_volatility = from_volatility + ehgf_increment(s, st, node, child, kappa);
     } else {  // :142-173
       const T gamma = HGF_S(child, F_EFFECTIVE_PRECISION);
       const T vope = HGF_S(child, F_VOLATILITY_PREDICTION_ERROR);
@@ -375,20 +382,20 @@ HGF_D T posterior_mean(const A& a, const T* s, int node, const T& node_precision
 }
 
 // continuous_node_posterior_update.py:20-128: precision, then mean.
-template <class T, class A> HGF_D void posterior_continuous(const A& a, T* s, const T& dt, int node, bool mean_field) {
+template <class T, class A> HGF_D void posterior_continuous(const A& a, T* s, const Step<T>& st, int node, bool mean_field) {
   using B = base_t<T>;
-  const T pi = x_min(posterior_precision(a, s, dt, node, mean_field, false), T(static_cast<B>(a.max_posterior_precision())));
+  const T pi = x_min(posterior_precision(a, s, st, node, mean_field, false), T(static_cast<B>(a.max_posterior_precision())));
   HGF_S(node, F_PRECISION) = pi;
   HGF_S(node, F_MEAN) = posterior_mean(a, s, node, pi, mean_field);
 }
 
 // continuous_node_posterior_update_ehgf.py:20-155: mean (with the expected
 // precision), then precision re-predicted from that mean.
-template <class T, class A> HGF_D void posterior_continuous_ehgf(const A& a, T* s, const T& dt, int node, bool mean_field) {
+template <class T, class A> HGF_D void posterior_continuous_ehgf(const A& a, T* s, const Step<T>& st, int node, bool mean_field) {
   using B = base_t<T>;
   HGF_S(node, F_MEAN) = posterior_mean(a, s, node, HGF_S(node, F_EXPECTED_PRECISION), mean_field);
   HGF_S(node, F_PRECISION) =
-      x_min(posterior_precision(a, s, dt, node, mean_field, true), T(static_cast<B>(a.max_posterior_precision())));
+      x_min(posterior_precision(a, s, st, node, mean_field, true), T(static_cast<B>(a.max_posterior_precision())));
 }
 
 // Quantities of the "unbounded" volatility-parent update that the child node
@@ -404,13 +411,13 @@ template <class T> struct VolatilityChild {
 // omega: EXPLICIT = false).  mu_hat / pi_hat are the volatility parent's (or
 // implicit volatility level's) prediction.
 template <bool EXPLICIT, class T>
-HGF_D void unbounded_mixture(const T& dt, const VolatilityChild<T>& c, const T& mu_hat, const T& pi_hat, const T& kappa,
+HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, const T& mu_hat, const T& pi_hat, const T& kappa,
                              const T& omega, T& post_precision, T& post_mean) {
   using B = base_t<T>;
   const T prev_var = x_max(c.prev_variance, T(static_cast<B>(1e-128)));
   const T delta = c.mean - c.expected_mean;
   const T be = B(1) / c.precision + delta * delta;  // E[(x - mu_hat)^2] under the child's posterior
-  const T log_dt = x_log(dt);
+  const T log_dt = st.log_dt;
   const T log_prev_var = x_log(prev_var);
   const T gamma = EXPLICIT ? (log_dt + kappa * mu_hat + omega) : (log_dt + mu_hat);
   // expansion 1: around the prediction
@@ -474,7 +481,7 @@ HGF_D void unbounded_mixture(const T& dt, const VolatilityChild<T>& c, const T& 
 
 // continuous_node_posterior_update_unbounded.py:13-48; reads only the first
 // volatility child (:71) and never its `observed` flag.
-template <class T, class A> HGF_D void posterior_continuous_unbounded(const A& a, T* s, const T& dt, int node) {
+template <class T, class A> HGF_D void posterior_continuous_unbounded(const A& a, T* s, const Step<T>& st, int node) {
   using B = base_t<T>;
   const int child = a.volc(node, 0);
   VolatilityChild<T> c;
@@ -484,7 +491,7 @@ template <class T, class A> HGF_D void posterior_continuous_unbounded(const A& a
   c.expected_mean = HGF_S(child, F_EXPECTED_MEAN);
   c.expected_precision = HGF_S(child, F_EXPECTED_PRECISION);
   T pi, mu;
-  unbounded_mixture<true>(dt, c, HGF_S(node, F_EXPECTED_MEAN), HGF_S(node, F_EXPECTED_PRECISION), s[a.slot_cvolc(node, 0)],
+  unbounded_mixture<true>(st, c, HGF_S(node, F_EXPECTED_MEAN), HGF_S(node, F_EXPECTED_PRECISION), s[a.slot_cvolc(node, 0)],
                           HGF_S(child, F_TONIC_VOLATILITY), pi, mu);
   HGF_S(node, F_PRECISION) = x_min(pi, T(static_cast<B>(a.max_posterior_precision())));
   HGF_S(node, F_MEAN) = mu;
@@ -534,7 +541,7 @@ template <class T, class A> HGF_D void posterior_volatile(const A& a, T* s, int 
 // (unbounded: volatile_node_posterior_update_unbounded.py:12-178; eHGF:
 // volatile_node_posterior_update_ehgf.py:16-75 + posterior_update_volatility_level.py;
 // standard: volatile_node_posterior_update.py:75-107).
-template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const T& dt, int node) {
+template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const Step<T>& st, int node) {
   using B = base_t<T>;
   const T delta = HGF_S(node, F_MEAN) - HGF_S(node, F_EXPECTED_MEAN);
   const T pi_hat = HGF_S(node, F_EXPECTED_PRECISION);
@@ -551,7 +558,7 @@ template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const T& dt
     c.expected_mean = HGF_S(node, F_EXPECTED_MEAN);
     c.expected_precision = pi_hat;
     T pi, mu;
-    unbounded_mixture<false>(dt, c, HGF_S(node, F_EXPECTED_MEAN_VOL), HGF_S(node, F_EXPECTED_PRECISION_VOL), T(B(1)), T(B(0)),
+    unbounded_mixture<false>(st, c, HGF_S(node, F_EXPECTED_MEAN_VOL), HGF_S(node, F_EXPECTED_PRECISION_VOL), T(B(1)), T(B(0)),
                              pi, mu);
     HGF_S(node, F_PRECISION_VOL) = x_min(pi, cap);
     HGF_S(node, F_MEAN_VOL) = mu;
@@ -560,7 +567,7 @@ template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const T& dt
     const T mean_vol = HGF_S(node, F_EXPECTED_MEAN_VOL) + (gamma * vope) / (B(2) * HGF_S(node, F_EXPECTED_PRECISION_VOL));
     HGF_S(node, F_MEAN_VOL) = mean_vol;
     const T prev_var = HGF_S(node, F_CURRENT_VARIANCE);
-    const T omega = dt * x_exp(mean_vol);
+    const T omega = st.dt * x_exp(mean_vol);
     const T pi_rep = B(1) / (prev_var + omega);
     const T gamma_rep = omega * pi_rep;
     const T weight = (omega - prev_var) * pi_rep;
@@ -579,21 +586,21 @@ template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const T& dt
 // ===========================================================================
 // One time slice -- pyhgf/utils/beliefs_propagation.py:24-159
 // ===========================================================================
-template <class T, class A> HGF_D void apply_op(const A& a, T* s, const T& dt, int op, int node) {
+template <class T, class A> HGF_D void apply_op(const A& a, T* s, const Step<T>& st, int op, int node) {
   switch (op) {
     case OP_PRED_BINARY: predict_binary(a, s, node); break;
-    case OP_PRED_CONT: predict_continuous(a, s, dt, node, false); break;
-    case OP_PRED_CONT_MF: predict_continuous(a, s, dt, node, true); break;
-    case OP_PRED_VOLATILE: predict_volatile(a, s, dt, node, false); break;
-    case OP_PRED_VOLATILE_MF: predict_volatile(a, s, dt, node, true); break;
+    case OP_PRED_CONT: predict_continuous(a, s, st, node, false); break;
+    case OP_PRED_CONT_MF: predict_continuous(a, s, st, node, true); break;
+    case OP_PRED_VOLATILE: predict_volatile(a, s, st, node, false); break;
+    case OP_PRED_VOLATILE_MF: predict_volatile(a, s, st, node, true); break;
     case OP_PE_BINARY: pe_binary(s, node); break;
     case OP_PE_CONT: pe_continuous(a, s, node); break;
-    case OP_PE_VOLATILE: pe_volatile(a, s, dt, node); break;
-    case OP_POST_CONT: posterior_continuous(a, s, dt, node, false); break;
-    case OP_POST_CONT_MF: posterior_continuous(a, s, dt, node, true); break;
-    case OP_POST_CONT_EHGF: posterior_continuous_ehgf(a, s, dt, node, false); break;
-    case OP_POST_CONT_EHGF_MF: posterior_continuous_ehgf(a, s, dt, node, true); break;
-    case OP_POST_CONT_UNBOUNDED: posterior_continuous_unbounded(a, s, dt, node); break;
+    case OP_PE_VOLATILE: pe_volatile(a, s, st, node); break;
+    case OP_POST_CONT: posterior_continuous(a, s, st, node, false); break;
+    case OP_POST_CONT_MF: posterior_continuous(a, s, st, node, true); break;
+    case OP_POST_CONT_EHGF: posterior_continuous_ehgf(a, s, st, node, false); break;
+    case OP_POST_CONT_EHGF_MF: posterior_continuous_ehgf(a, s, st, node, true); break;
+    case OP_POST_CONT_UNBOUNDED: posterior_continuous_unbounded(a, s, st, node); break;
     case OP_POST_VOLATILE: posterior_volatile(a, s, node, false); break;
     case OP_POST_VOLATILE_MF: posterior_volatile(a, s, node, true); break;
     default: break;
@@ -620,39 +627,57 @@ template <class T> HGF_D T gaussian_surprise(const T& x, const T& mu_hat, const 
 
 template <class T> HGF_D T nan_to_inf(const T& x) { return x_isnan(x) ? T(b_inf<base_t<T>>()) : x; }
 
-template <class T, class A> HGF_D T response_step(const A& a, const T* s, int response_fn, base_t<T> resp_input) {
+// Widen a filter scalar to the response function's scalar: same value and leading tangents, the extra
+// (response-parameter) tangent directions start at zero.
+template <class TR, class T> HGF_D TR widen(const T& x) {
+  if constexpr (scalar_traits<TR>::n_tangents == scalar_traits<T>::n_tangents) {
+    return x;
+  } else {
+    TR r(pv(x));
+#pragma unroll
+    for (int i = 0; i < scalar_traits<T>::n_tangents; ++i) r.d[i] = x.d[i];
+    return r;
+  }
+}
+
+// `s` holds the beliefs in the filter's scalar T; `rp` the response-function parameters in the
+// response scalar TR (which may carry more tangent directions than T).
+template <class TR, class T, class A>
+HGF_D TR response_step(const A& a, const T* s, const TR* rp, int response_fn, base_t<T> resp_input) {
   using B = base_t<T>;
+#define HGF_R(node, field) widen<TR>(HGF_S(node, field))
   switch (response_fn) {
     case RESP_FIRST_LEVEL_GAUSSIAN:  // node 0's observation against node 1's prediction, response.py:41-48
-      return nan_to_inf(gaussian_surprise(HGF_S(0, F_MEAN), HGF_S(1, F_EXPECTED_MEAN), HGF_S(1, F_EXPECTED_PRECISION)));
+      return nan_to_inf(gaussian_surprise(HGF_R(0, F_MEAN), HGF_R(1, F_EXPECTED_MEAN), HGF_R(1, F_EXPECTED_PRECISION)));
     case RESP_TOTAL_GAUSSIAN: {  // response.py:51-89 (its any-NaN rule is applied by the caller)
-      T total = T(B(0));
+      TR total = TR(B(0));
 #pragma unroll (A::kUnroll)
       for (int n = 0; n < a.n_nodes(); ++n)
         if (a.node_type(n) == NODE_CONTINUOUS)
-          total = total + gaussian_surprise(HGF_S(n, F_MEAN), HGF_S(n, F_EXPECTED_MEAN), HGF_S(n, F_EXPECTED_PRECISION));
+          total = total + gaussian_surprise(HGF_R(n, F_MEAN), HGF_R(n, F_EXPECTED_MEAN), HGF_R(n, F_EXPECTED_PRECISION));
       return total;
     }
     case RESP_FIRST_LEVEL_BINARY: {  // response.py:92-130
-      T total = T(B(0));
+      TR total = TR(B(0));
 #pragma unroll (A::kUnroll)
       for (int k = 0; k < a.n_inputs(); ++k) {
         const int n = a.input_idx(k);
-        total = total + binary_surprise(pv(HGF_S(n, F_MEAN)) != B(0), HGF_S(n, F_EXPECTED_MEAN));
+        total = total + binary_surprise(pv(HGF_S(n, F_MEAN)) != B(0), HGF_R(n, F_EXPECTED_MEAN));
       }
       return nan_to_inf(total);
     }
     case RESP_BINARY_SOFTMAX:  // response.py:133-164
-      return nan_to_inf(binary_surprise(resp_input != B(0), HGF_S(0, F_EXPECTED_MEAN)));
+      return nan_to_inf(binary_surprise(resp_input != B(0), HGF_R(0, F_EXPECTED_MEAN)));
     case RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE: {  // response.py:167-215
-      const T mu = HGF_S(0, F_EXPECTED_MEAN);
-      const T temp = s[a.slot_resp()];
-      const T p1 = x_pow(mu, temp);
-      const T p0 = x_pow(B(1) - mu, temp);
+      const TR mu = HGF_R(0, F_EXPECTED_MEAN);
+      const TR temp = rp[0];
+      const TR p1 = x_pow(mu, temp);
+      const TR p0 = x_pow(B(1) - mu, temp);
       return nan_to_inf(binary_surprise(resp_input != B(0), p1 / (p1 + p0)));
     }
-    default: return T(B(0));
+    default: return TR(B(0));
   }
+#undef HGF_R
 }
 
 }  // namespace hgf

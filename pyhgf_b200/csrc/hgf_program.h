@@ -78,10 +78,17 @@ struct Program {
 };
 
 // Per-call lists (which leaves are recorded, which slots are per-instance).
+// Parameters are kept in launch order: the first n_filter are seeded into the
+// attribute vector and carry their tangents through the whole filter; the rest
+// are response-function parameters, which cannot influence the beliefs, so their
+// tangents exist only inside the response function (Dual<PF + PR> there,
+// Dual<PF> in the filter).  param_row[q] is the parameter's row in the caller's
+// params / gradient arrays.
 struct CallLists {
-  int32_t n_rec, n_params;
+  int32_t n_rec, n_params, n_filter;
   uint16_t rec_slot[MAX_RECORDS];
   uint16_t param_slot[MAX_PARAMS];
+  uint16_t param_row[MAX_PARAMS];
 };
 
 // One launch's arguments (device pointers; see hgf_call_t in include/pyhgf_cuda.h).
@@ -104,7 +111,8 @@ struct ScanArgs {
   const int32_t* group;
   double out_scale;
   int response_fn;
-  int tangent_offset;  // this pass differentiates params [tangent_offset, tangent_offset + P)
+  int tangent_offset;  // this pass differentiates the filter params [tangent_offset, tangent_offset + PF)
+  int resp_index;      // ... and the response-function param at this position of the lists (-1: none)
   // register-resident specialisations: which belief leaves (mean, expected_mean, precision,
   // expected_precision per node, + the *_vol twins of volatile nodes, in slot order) are recorded;
   // leaf r is stored in trajectory row popcount(mask below r)

@@ -6,19 +6,30 @@
 // flat partition of the batch; every global access is coalesced over instances
 // (parameters [P][N], trajectories [R][T][N], outputs [.][N]); the observation
 // series is uniform across a warp (broadcast loads).
+//
+// Template parameters:
+//   T       Dual<B, PF>: the filter's scalar (PF tangent directions; 0 = plain filter)
+//   PR      extra tangent directions that exist only inside the response function
+//           (response-function parameters cannot influence the beliefs)
+//   UNIT_DT the call has no time_steps vector: dt = 1, log dt = 0 fold away
 #pragma once
 #include "hgf_ops.cuh"
 
 namespace hgf {
 
-constexpr int SCAN_THREADS = 128;
+constexpr int SCAN_THREADS = 64;
 
-// One instance, all time steps.  Returns out_scale-free summed surprise (with
-// its tangents); every per-instance output is stored here when `active`.
-template <class T, class Topo, int NSLOTS>
-HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArgs& args, long long n, bool active) {
+template <class T, int PR> struct response_scalar { using type = Dual<base_t<T>, scalar_traits<T>::n_tangents + PR>; };
+template <class T, int PR> using response_scalar_t = typename response_scalar<T, PR>::type;
+
+// One instance, all time steps.  Returns the summed surprise (with its tangents);
+// every per-instance output is stored here when `active`.
+template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT>
+HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallLists& lists, const ScanArgs& args, long long n,
+                                             bool active) {
   using B = base_t<T>;
-  constexpr int P = scalar_traits<T>::n_tangents;
+  using TR = response_scalar_t<T, PR>;
+  constexpr int PF = scalar_traits<T>::n_tangents;
   const Topo a(prog);
   const long long N = args.n_instances;
 
@@ -34,14 +45,14 @@ HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArg
     for (int k = 0; k < n_slots; ++k) s[k] = T(HGF_LDG(base + k));
   }
   const B* params = static_cast<const B*>(args.params);
-  for (int p = 0; p < lists.n_params; ++p) {
-    T v = T(HGF_LDG(params + static_cast<long long>(p) * N + n));
-    if constexpr (P > 0) {
+  for (int q = 0; q < lists.n_filter; ++q) {
+    T v = T(HGF_LDG(params + static_cast<long long>(lists.param_row[q]) * N + n));
+    if constexpr (PF > 0) {
 #pragma unroll
-      for (int i = 0; i < P; ++i)
-        if (i == p - args.tangent_offset) v.d[i] = B(1);
+      for (int i = 0; i < PF; ++i)
+        if (i == q - args.tangent_offset) v.d[i] = B(1);
     }
-    const int slot = lists.param_slot[p];
+    const int slot = lists.param_slot[q];
     if constexpr (Topo::is_static) {
 #pragma unroll
       for (int k = 0; k < NSLOTS; ++k)
@@ -49,6 +60,20 @@ HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArg
     } else {
       s[slot] = v;
     }
+  }
+  // response-function parameters (the trailing entries of the lists override the shared values)
+  TR rp[N_RESP_PARAMS];
+#pragma unroll
+  for (int j = 0; j < N_RESP_PARAMS; ++j) rp[j] = widen<TR>(s[a.slot_resp() + j]);
+  for (int q = lists.n_filter; q < lists.n_params; ++q) {
+    TR v = TR(HGF_LDG(params + static_cast<long long>(lists.param_row[q]) * N + n));
+    if constexpr (PR > 0) {
+      if (q == args.resp_index) v.d[PF] = B(1);
+    }
+    const int j = lists.param_slot[q] - a.slot_resp();
+#pragma unroll
+    for (int jj = 0; jj < N_RESP_PARAMS; ++jj)
+      if (jj == j) rp[jj] = v;
   }
 
   const int T_steps = args.n_steps;
@@ -66,14 +91,21 @@ HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArg
   B* pointwise = static_cast<B*>(args.surprise_pointwise);
   const int response_fn = args.response_fn;
 
-  T total = T(B(0));
+  TR total = TR(B(0));
   bool node1_mean_nan = false;
 
   for (int t = 0; t < T_steps; ++t) {
-    const T dt = T(time_steps ? HGF_LDG(time_steps + t) : B(1));
+    Step<T> st;
+    if constexpr (UNIT_DT) {
+      st.dt = T(B(1));
+      st.log_dt = T(B(0));
+    } else {
+      st.dt = T(time_steps ? HGF_LDG(time_steps + t) : B(1));
+      st.log_dt = x_log(st.dt);
+    }
     // prediction sequence (parents before children)
 #pragma unroll (Topo::kUnroll)
-    for (int i = 0; i < a.n_pred(); ++i) apply_op(a, s, dt, a.pred_op(i), a.pred_node(i));
+    for (int i = 0; i < a.n_pred(); ++i) apply_op(a, s, st, a.pred_op(i), a.pred_node(i));
     // set_observation, pyhgf/updates/observation.py:10-38
 #pragma unroll (Topo::kUnroll)
     for (int k = 0; k < n_fed; ++k) {
@@ -83,10 +115,10 @@ HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArg
     }
     // prediction errors and posterior updates (children before parents)
 #pragma unroll (Topo::kUnroll)
-    for (int i = 0; i < a.n_upd(); ++i) apply_op(a, s, dt, a.upd_op(i), a.upd_node(i));
+    for (int i = 0; i < a.n_upd(); ++i) apply_op(a, s, st, a.upd_op(i), a.upd_node(i));
 
     if (response_fn != RESP_NONE) {
-      const T r = response_step(a, s, response_fn, resp ? HGF_LDG(resp + t) : B(0));
+      const TR r = response_step<TR>(a, s, rp, response_fn, resp ? HGF_LDG(resp + t) : B(0));
       total = total + r;
       if (pointwise && active) pointwise[static_cast<long long>(t) * N + n] = pv(r);
       if (response_fn == RESP_TOTAL_GAUSSIAN && a.n_nodes() > 1 && x_isnan(HGF_S(1, F_MEAN))) node1_mean_nan = true;
@@ -114,18 +146,21 @@ HGF_D T scan_instance(const Program& prog, const CallLists& lists, const ScanArg
   }
 
   // response.py:87-89: total_gaussian_surprise is +inf everywhere if node 1's mean ever was NaN
-  if (response_fn == RESP_TOTAL_GAUSSIAN && node1_mean_nan) total = T(b_inf<B>());
+  if (response_fn == RESP_TOTAL_GAUSSIAN && node1_mean_nan) total = TR(b_inf<B>());
 
   const B scale = static_cast<B>(args.out_scale);
   if (active) {
     if (args.surprise_sum) static_cast<B*>(args.surprise_sum)[n] = scale * pv(total);
-    if constexpr (P > 0) {
-      if (args.gradient) {
-        B* grad = static_cast<B*>(args.gradient);
+    if (args.gradient) {
+      B* grad = static_cast<B*>(args.gradient);
+      if constexpr (PF > 0) {
 #pragma unroll
-        for (int i = 0; i < P; ++i)
-          if (args.tangent_offset + i < lists.n_params)
-            grad[static_cast<long long>(args.tangent_offset + i) * N + n] = scale * total.d[i];
+        for (int i = 0; i < PF; ++i)
+          if (args.tangent_offset + i < lists.n_filter)
+            grad[static_cast<long long>(lists.param_row[args.tangent_offset + i]) * N + n] = scale * total.d[i];
+      }
+      if constexpr (PR > 0) {
+        if (args.resp_index >= 0) grad[static_cast<long long>(lists.param_row[args.resp_index]) * N + n] = scale * total.d[PF];
       }
     }
     if (args.last_attributes) {
@@ -158,14 +193,14 @@ template <class B> __device__ __forceinline__ void reduce_into_groups(B* reduced
   }
 }
 
-template <class T, class Topo, int NSLOTS>
+template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT>
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLists lists, const __grid_constant__ ScanArgs args) {
   using B = base_t<T>;
   long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool active = n < args.n_instances;
   if (!active) n = args.n_instances - 1;  // keep the warp whole for the shuffle reduction; stores are predicated
-  const T total = scan_instance<T, Topo, NSLOTS>(prog, lists, args, n, active);
+  const auto total = scan_instance<T, Topo, NSLOTS, PR, UNIT_DT>(prog, lists, args, n, active);
   if (args.reduced) {
     const int g = args.group ? __ldg(args.group + n) : 0;
     reduce_into_groups<B>(static_cast<B*>(args.reduced), g, static_cast<B>(args.out_scale) * pv(total), active);

@@ -67,42 +67,18 @@ bool static_record_mask(const Program& p, const CallLists& lists, uint32_t mask[
   return true;
 }
 
-// MASK bit k: the Dual<B, k> kernel of this topology was instantiated (bit 0: the plain filter).
+// MASK: the (PF, PR) kernels of this topology that were instantiated (variant_bit in hgf_launch_decl.h).
 template <class B, class Topo, unsigned MASK>
 cudaError_t run_static(const Program& prog, const CallLists& lists, const ScanArgs& args_in, int dtype, bool want_grad,
                        cudaStream_t stream, int* n_launched) {
   ScanArgs args = args_in;
   const bool rec_ok = !args.trajectories || static_record_mask<Topo>(prog, lists, args.rec_mask);
-  const bool have = want_grad ? (MASK & 0x1eu) != 0 : (MASK & 1u) != 0;
-  if (!rec_ok || !have) return kInterpreterVariant.run(prog, lists, args_in, dtype, want_grad, stream, n_launched);
-  if (!want_grad) {
-    ++*n_launched;
-    if constexpr ((MASK & 1u) != 0) return launch_one<Dual<B, 0>, Topo, Topo::kSlots>(prog, lists, args, stream);
-    return cudaErrorInvalidValue;
+  if (rec_ok) {
+    const int before = *n_launched;
+    const cudaError_t err = launch_scan<B, Topo, Topo::kSlots, MASK>(prog, lists, args, want_grad, stream, n_launched);
+    if (err != cudaErrorNotSupported || *n_launched != before) return err;
   }
-  int done = 0;
-  while (done < lists.n_params) {
-    const int rem = lists.n_params - done;
-    int w = 0;
-    for (int k = 4; k >= 1; --k)
-      if ((MASK >> k & 1u) && k <= rem) { w = k; break; }
-    if (!w)
-      for (int k = 1; k <= 4; ++k)
-        if (MASK >> k & 1u) { w = k; break; }
-    args.tangent_offset = done;
-    cudaError_t err = cudaErrorInvalidValue;
-    if constexpr ((MASK >> 1 & 1u) != 0) { if (w == 1) err = launch_one<Dual<B, 1>, Topo, Topo::kSlots>(prog, lists, args, stream); }
-    if constexpr ((MASK >> 2 & 1u) != 0) { if (w == 2) err = launch_one<Dual<B, 2>, Topo, Topo::kSlots>(prog, lists, args, stream); }
-    if constexpr ((MASK >> 3 & 1u) != 0) { if (w == 3) err = launch_one<Dual<B, 3>, Topo, Topo::kSlots>(prog, lists, args, stream); }
-    if constexpr ((MASK >> 4 & 1u) != 0) { if (w == 4) err = launch_one<Dual<B, 4>, Topo, Topo::kSlots>(prog, lists, args, stream); }
-    ++*n_launched;
-    if (err != cudaSuccess) return err;
-    done += w;
-    // later passes only add gradient columns
-    args.trajectories = nullptr; args.last_attributes = nullptr; args.surprise_sum = nullptr; args.surprise_pointwise = nullptr;
-    args.reduced = nullptr;
-  }
-  return cudaSuccess;
+  return kInterpreterVariant.run(prog, lists, args_in, dtype, want_grad, stream, n_launched);
 }
 
 template <class Topo, unsigned MASK32, unsigned MASK64>
