@@ -154,7 +154,7 @@ def generate_topology(name, spec) -> str:
     out = [
         f"// GENERATED by pyhgf_b200/codegen.py -- topology \"{name}\" ({n} nodes, volatility_updates={vol_updates}).\n",
         "// Compile-time answers to the topology queries of hgf_ops.cuh; do not edit.\n",
-        "#pragma once\n#include \"hgf_math.cuh\"\n#include \"hgf_program.h\"\n\nnamespace hgf {\n\n",
+        "#pragma once\n#include \"hgf_ops.cuh\"\n\nnamespace hgf {\n\n",
         f"struct Topo_{name} {{\n",
         "  static constexpr bool is_static = true;\n  static constexpr int kUnroll = 256;\n",
         f"  static constexpr int kSlots = {n_slots};\n  static constexpr int kNodes = {n};\n",
@@ -185,7 +185,15 @@ def generate_topology(name, spec) -> str:
         out.append(_switch(fn, ["n"], {(i,): c for i, c in enumerate(counts[key]) if c}))
     for fn in ("vp", "vp_fn", "volp", "vc", "vc_fn", "volc", "slot_cvp", "slot_cvolp", "slot_cvc", "slot_cvolc"):
         out.append(_switch(fn, ["n", "k"], t[fn]))
-    out.append("};\n\n}  // namespace hgf\n")
+    # the schedule as straight-line code: every op and node index is a literal, so the switch in apply_op and
+    # the edge loops inside the update functions resolve at compile time without relying on loop unrolling
+    out.append("  template <class T> HGF_D void run_predictions(T* s, const Step<T>& st) const {\n")
+    for node, fn in pred:
+        out.append(f"    apply_op(*this, s, st, {fn.opcode}, {node});  // {fn.__name__}\n")
+    out.append("  }\n  template <class T> HGF_D void run_updates(T* s, const Step<T>& st) const {\n")
+    for node, fn in upd:
+        out.append(f"    apply_op(*this, s, st, {fn.opcode}, {node});  // {fn.__name__}\n")
+    out.append("  }\n};\n\n}  // namespace hgf\n")
     return "".join(out)
 
 

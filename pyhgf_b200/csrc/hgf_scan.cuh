@@ -104,8 +104,11 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
       st.log_dt = x_log(st.dt);
     }
     // prediction sequence (parents before children)
-#pragma unroll (Topo::kUnroll)
-    for (int i = 0; i < a.n_pred(); ++i) apply_op(a, s, st, a.pred_op(i), a.pred_node(i));
+    if constexpr (Topo::is_static) {
+      a.run_predictions(s, st);
+    } else {
+      for (int i = 0; i < a.n_pred(); ++i) apply_op(a, s, st, a.pred_op(i), a.pred_node(i));
+    }
     // set_observation, pyhgf/updates/observation.py:10-38
 #pragma unroll (Topo::kUnroll)
     for (int k = 0; k < n_fed; ++k) {
@@ -114,8 +117,11 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
       HGF_S(node, F_OBSERVED) = T(obs ? static_cast<B>(HGF_LDG(obs + static_cast<long long>(t) * n_fed + k)) : B(1));
     }
     // prediction errors and posterior updates (children before parents)
-#pragma unroll (Topo::kUnroll)
-    for (int i = 0; i < a.n_upd(); ++i) apply_op(a, s, st, a.upd_op(i), a.upd_node(i));
+    if constexpr (Topo::is_static) {
+      a.run_updates(s, st);
+    } else {
+      for (int i = 0; i < a.n_upd(); ++i) apply_op(a, s, st, a.upd_op(i), a.upd_node(i));
+    }
 
     if (response_fn != RESP_NONE) {
       const TR r = response_step<TR>(a, s, rp, response_fn, resp ? HGF_LDG(resp + t) : B(0));
@@ -163,13 +169,12 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
         if (args.resp_index >= 0) grad[static_cast<long long>(lists.param_row[args.resp_index]) * N + n] = scale * total.d[PF];
       }
     }
-    if (args.last_attributes) {
-      B* last = static_cast<B*>(args.last_attributes);
-      if constexpr (Topo::is_static) {
-#pragma unroll
-        for (int k = 0; k < NSLOTS; ++k)
-          if (k < a.n_nodes() * NF) last[static_cast<long long>(k) * N + n] = pv(s[k]);
-      } else {
+    // the final attribute vector is an interpreter-only output (hgf_static_run.h routes such calls there):
+    // keeping all n_nodes x 19 fields alive to the end of the loop would cost the register-resident
+    // kernels their registers
+    if constexpr (!Topo::is_static) {
+      if (args.last_attributes) {
+        B* last = static_cast<B*>(args.last_attributes);
         for (int k = 0; k < a.n_nodes() * NF; ++k) last[static_cast<long long>(k) * N + n] = pv(s[k]);
       }
     }
@@ -193,8 +198,16 @@ template <class B> __device__ __forceinline__ void reduce_into_groups(B* reduced
   }
 }
 
+// Occupancy: BASELINE config 4 gives each GPU 65 536 instances = 13.8 warps per SM; the float32 register-
+// resident kernels are bounded to 7 resident 64-thread blocks (<= 144 registers) so that the whole batch
+// is co-resident in one wave instead of 1.7 (a second, mostly empty wave costs ~40 %).
+template <class T, class Topo> constexpr int scan_min_blocks() {
+  if constexpr (!Topo::is_static) return 1; else
+  return (Topo::is_static && sizeof(base_t<T>) == 4 && Topo::kNodes <= 4) ? 7 : 1;
+}
+
 template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT>
-__global__ void __launch_bounds__(SCAN_THREADS)
+__global__ void __launch_bounds__(SCAN_THREADS, scan_min_blocks<T, Topo>())
 scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLists lists, const __grid_constant__ ScanArgs args) {
   using B = base_t<T>;
   long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;

@@ -3,8 +3,9 @@
 //                            specialisation was generated for?
 //   * run_static<...>     -- dispatch to the instantiated kernels of that topology
 //                            (falling back to the interpreter for scalar types that
-//                            were not instantiated, or for record sets outside the
-//                            specialisation's belief leaves).
+//                            were not instantiated, for record sets outside the
+//                            specialisation's belief leaves, or when the final
+//                            attribute vector is requested).
 #pragma once
 #include "hgf_dispatch.h"
 #include "hgf_launch_decl.h"
@@ -72,7 +73,7 @@ template <class B, class Topo, unsigned MASK>
 cudaError_t run_static(const Program& prog, const CallLists& lists, const ScanArgs& args_in, int dtype, bool want_grad,
                        cudaStream_t stream, int* n_launched) {
   ScanArgs args = args_in;
-  const bool rec_ok = !args.trajectories || static_record_mask<Topo>(prog, lists, args.rec_mask);
+  const bool rec_ok = !args.last_attributes && (!args.trajectories || static_record_mask<Topo>(prog, lists, args.rec_mask));
   if (rec_ok) {
     const int before = *n_launched;
     const cudaError_t err = launch_scan<B, Topo, Topo::kSlots, MASK>(prog, lists, args, want_grad, stream, n_launched);
