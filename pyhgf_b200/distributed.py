@@ -1,0 +1,107 @@
+"""Instance-sharded evaluation across the GPUs of one box.
+
+Network instances are independent (no exchange inside the time loop), so the
+batch shards contiguously over ranks -- by participant for grouped inputs, so
+that a participant's series and all its chains live on one GPU -- with no
+data-path collective.  The only exchange is the sum of the per-group (per-chain)
+log-probabilities and of gradients of *shared* parameters: one small
+all-reduce over NCCL / NVLink (``torch.distributed``), enqueued on the stream
+of the kernel that produced the sums.  The reference has no multi-device path
+("Parallelism strategies"): this layer is new.
+"""
+
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(n_items: int, world_size: int, rank: int) -> tuple:
+    """Contiguous, balanced partition: the first ``n_items % world_size`` ranks get one extra item."""
+    if world_size < 1 or not 0 <= rank < world_size:
+        raise ValueError("invalid rank / world_size")
+    base, extra = divmod(n_items, world_size)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_groups(n_groups: int, group_size: int, world_size: int, rank: int) -> tuple:
+    """Shard whole groups (participants); returns (first group, last group, first instance, last instance)."""
+    g0, g1 = shard_bounds(n_groups, world_size, rank)
+    return g0, g1, g0 * group_size, g1 * group_size
+
+
+def all_reduce_sums(tensors: Sequence[torch.Tensor], group: Optional[dist.ProcessGroup] = None) -> None:
+    """Sum small per-chain / shared-parameter tensors over ranks, in place (one flat all-reduce)."""
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    tensors = [t for t in tensors if t is not None]
+    if not tensors:
+        return
+    if len(tensors) == 1:
+        dist.all_reduce(tensors[0], op=dist.ReduceOp.SUM, group=group)
+        return
+    flat = torch.cat([t.reshape(-1) for t in tensors])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    off = 0
+    for t in tensors:
+        t.copy_(flat[off:off + t.numel()].view_as(t))
+        off += t.numel()
+
+
+class ShardedLogp:
+    """``HGFDistribution`` over the ranks of a process group.
+
+    Every rank constructs it with the FULL ``input_data`` / ``response_function_inputs`` ``(N, T)`` and
+    calls it with FULL parameter arrays ``(N,)`` / ``(N, n_chains)``; each rank evaluates its contiguous
+    block of participants on its own GPU and the per-chain sums are all-reduced.  Per-participant
+    gradients stay sharded (``local_slice`` tells which rows a rank owns).
+    """
+
+    def __init__(self, input_data, response_function, response_function_inputs=None, *, n_chains: int = 1, group=None,
+                 evaluator_factory=None, **kwargs):
+        self.group = group
+        initialised = dist.is_available() and dist.is_initialized()
+        self.world = dist.get_world_size(group) if initialised else 1
+        self.rank = dist.get_rank(group) if initialised else 0
+        n = len(input_data)
+        self.lo, self.hi = shard_bounds(n, self.world, self.rank)
+        self.n_participants, self.n_chains = n, n_chains
+        if evaluator_factory is None:
+            from .distribution import HGFDistribution as evaluator_factory
+        resp = None if response_function_inputs is None else response_function_inputs[self.lo:self.hi]
+        self.local = evaluator_factory(input_data=input_data[self.lo:self.hi], response_function=response_function,
+                                       response_function_inputs=resp, n_chains=n_chains, **kwargs)
+
+    @property
+    def local_slice(self) -> slice:
+        return slice(self.lo, self.hi)
+
+    def _local_params(self, params: dict) -> dict:
+        out = {}
+        for k, v in params.items():
+            shape = tuple(getattr(v, "shape", ()))
+            out[k] = v[self.lo:self.hi] if len(shape) >= 1 and shape[0] == self.n_participants else v
+        return out
+
+    def __call__(self, **params):
+        total = self.local(**self._local_params(params))
+        total = total.clone() if torch.is_tensor(total) else torch.as_tensor(total)
+        all_reduce_sums([total], self.group)
+        return total
+
+    def value_and_grad(self, **params):
+        """(all-reduced sum of logp [per chain], {name: gradient}); gradients of per-participant parameters
+        are this rank's rows, gradients of shared (scalar / per-chain) parameters are all-reduced."""
+        total, grads = self.local.value_and_grad(**self._local_params(params))
+        total = total.clone()
+        shared = []
+        for k, v in params.items():
+            shape = tuple(getattr(v, "shape", ()))
+            if not (len(shape) >= 1 and shape[0] == self.n_participants):
+                grads[k] = grads[k].clone()
+                shared.append(grads[k])
+        all_reduce_sums([total] + shared, self.group)
+        return total, grads
