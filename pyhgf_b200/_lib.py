@@ -10,7 +10,9 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libpyhgf_cuda.so")
+# HGF_MATH=accurate loads the validation build (IEEE division, libdevice transcendentals, no FMA contraction:
+# `HGF_MATH=accurate python -m pyhgf_b200.build`); the shipped library is the default.
+LIB_PATH = os.path.join(_HERE, "lib", "libpyhgf_cuda_accurate.so" if os.environ.get("HGF_MATH") == "accurate" else "libpyhgf_cuda.so")
 
 N_FIELDS = 19
 N_RESPONSE_PARAMETERS = 4

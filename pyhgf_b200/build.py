@@ -19,15 +19,14 @@ import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "pyhgf_b200", "csrc")
-OBJ = os.path.join(ROOT, "build", "obj")
-LIB = os.path.join(ROOT, "pyhgf_b200", "lib", "libpyhgf_cuda.so")
-
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 #: "sfu" (default): MUFU-based float32 division/exp/log, FMA contraction; "accurate": IEEE division, libdevice
 #: transcendentals, one rounding per primitive (the validation build) -- see csrc/hgf_math.cuh
 MATH = os.environ.get("HGF_MATH", "sfu")
 if MATH not in ("sfu", "accurate"):
     raise SystemExit("HGF_MATH must be 'sfu' or 'accurate'")
+OBJ = os.path.join(ROOT, "build", "obj" if MATH == "sfu" else "obj_accurate")
+LIB = os.path.join(ROOT, "pyhgf_b200", "lib", "libpyhgf_cuda.so" if MATH == "sfu" else "libpyhgf_cuda_accurate.so")
 COMMON = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
     "-Xcompiler", "-fPIC", "-diag-suppress", "221", "-I", CSRC, "-I", os.path.join(ROOT, "include"),
@@ -69,17 +68,23 @@ def jobs():
     return out
 
 
-def _stale(src, obj, flags, dep_mtime):
+def _stamp(src, flags, dep_hash):
+    """Content stamp of one translation unit: flags + source + every header (mtimes do not survive the copy
+    to the GPU box, so staleness is decided on content)."""
+    h = hashlib.sha1(" ".join(COMMON + flags).encode())
+    h.update(open(src, "rb").read())
+    h.update(dep_hash.encode())
+    return h.hexdigest()
+
+
+def _stale(src, obj, flags, dep_hash):
     if not os.path.exists(obj):
         return True
     stamp = obj + ".flags"
-    want = hashlib.sha1(" ".join(COMMON + flags).encode()).hexdigest()
-    if not os.path.exists(stamp) or open(stamp).read() != want:
-        return True
-    return os.path.getmtime(obj) < max(os.path.getmtime(src), dep_mtime)
+    return not os.path.exists(stamp) or open(stamp).read() != _stamp(src, flags, dep_hash)
 
 
-def _compile(job, verbose):
+def _compile(job, verbose, dep_hash):
     src, obj, flags = job
     t0 = time.time()
     cmd = [NVCC] + COMMON + flags + ["-c", src, "-o", obj]
@@ -87,7 +92,7 @@ def _compile(job, verbose):
     if r.returncode != 0:
         raise RuntimeError(f"nvcc failed for {os.path.basename(obj)}:\n{r.stdout}\n{r.stderr}")
     with open(obj + ".flags", "w") as f:
-        f.write(hashlib.sha1(" ".join(COMMON + flags).encode()).hexdigest())
+        f.write(_stamp(src, flags, dep_hash))
     if verbose:
         print(f"  [{time.time() - t0:6.1f}s] {os.path.basename(obj)}", flush=True)
     return obj
@@ -99,25 +104,32 @@ def build(force: bool = False, n_jobs: int | None = None, verbose: bool = True) 
     gen_script = os.path.join(ROOT, "pyhgf_b200", "codegen.py")
     if os.path.exists(gen_script):
         subprocess.run([sys.executable, "-m", "pyhgf_b200.codegen"], check=True, cwd=ROOT)
-    dep_mtime = max(os.path.getmtime(h) for h in _headers())
+    deps = _headers()
     gen = os.path.join(CSRC, "generated")
     if os.path.isdir(gen):
-        for f in os.listdir(gen):
-            dep_mtime = max(dep_mtime, os.path.getmtime(os.path.join(gen, f)))
+        deps += [os.path.join(gen, f) for f in sorted(os.listdir(gen))]
+    dh = hashlib.sha1()
+    for d in deps:
+        dh.update(open(d, "rb").read())
+    dep_hash = dh.hexdigest()
     all_jobs = jobs()
-    todo = [j for j in all_jobs if force or _stale(j[0], j[1], j[2], dep_mtime)]
+    todo = [j for j in all_jobs if force or _stale(j[0], j[1], j[2], dep_hash)]
     if verbose:
         print(f"pyhgf_b200.build: {len(todo)} of {len(all_jobs)} translation units to compile", flush=True)
     n_jobs = n_jobs or os.cpu_count() or 4
     if todo:
         with cf.ThreadPoolExecutor(max_workers=n_jobs) as ex:
-            list(ex.map(lambda j: _compile(j, verbose), todo))
+            list(ex.map(lambda j: _compile(j, verbose, dep_hash), todo))
     objs = [j[1] for j in all_jobs]
-    if todo or not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(o) for o in objs):
+    link_stamp = LIB + ".stamp"
+    want_link = hashlib.sha1("".join(open(o + ".flags").read() for o in objs).encode()).hexdigest()
+    if todo or not os.path.exists(LIB) or not os.path.exists(link_stamp) or open(link_stamp).read() != want_link:
         cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+        with open(link_stamp, "w") as f:
+            f.write(want_link)
         if verbose:
             print(f"pyhgf_b200.build: linked {LIB}", flush=True)
     return LIB
