@@ -9,6 +9,9 @@
 #include <string>
 #include <vector>
 
+#include <cuda.h>  // CUtensorMap (types only: the encoder is fetched with cudaGetDriverEntryPoint, no libcuda link)
+#include <cstdlib>
+
 #include "../../include/pyhgf_cuda.h"
 #include "hgf_dispatch.h"
 
@@ -210,6 +213,42 @@ static int check_call(const hgf_plan_t* plan, const hgf_call_t* c, bool want_gra
   return 0;
 }
 
+// Tensor map of trajectories[R][T][N] for the kernels' TMA write-back (ScanArgs::traj_map): dims (N, T, R),
+// box (SCAN_THREADS instances, 1 step, R leaves).  Returns false when the array does not meet TMA's
+// alignment rules or the staging tile would not fit -- the kernel then uses plain coalesced stores.
+static bool encode_trajectory_map(ScanArgs& a, int n_rec, int width) {
+  const char* env = std::getenv("HGF_NO_TMA");  // read per call: the tests run both write-back paths in one process
+  const bool disabled = env && env[0] == '1';
+  constexpr int kThreads = 64;  // SCAN_THREADS (hgf_scan.cuh)
+  if (disabled || n_rec < 1 || n_rec > 256) return false;
+  if (2ull * n_rec * kThreads * width > 96 * 1024) return false;
+  if ((a.n_instances * width) % 16 != 0 || reinterpret_cast<uintptr_t>(a.trajectories) % 16 != 0) return false;
+  if (a.n_instances > 0x7fffffffLL || a.n_steps < 1) return false;
+  using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+      fn = nullptr;
+    return reinterpret_cast<EncodeFn>(fn);
+  }();
+  if (!encode) return false;
+  static_assert(sizeof(CUtensorMap) == sizeof(a.traj_map), "CUtensorMap size");
+  const cuuint64_t dims[3] = {static_cast<cuuint64_t>(a.n_instances), static_cast<cuuint64_t>(a.n_steps), static_cast<cuuint64_t>(n_rec)};
+  const cuuint64_t strides[2] = {static_cast<cuuint64_t>(a.n_instances) * width,
+                                 static_cast<cuuint64_t>(a.n_instances) * a.n_steps * width};
+  const cuuint32_t box[3] = {kThreads, 1, static_cast<cuuint32_t>(n_rec)};
+  const cuuint32_t elem[3] = {1, 1, 1};
+  const CUresult r = encode(reinterpret_cast<CUtensorMap*>(a.traj_map), width == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64,
+                            3, a.trajectories, dims, strides, box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                            CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return false;
+  a.traj_rows = n_rec;
+  return true;
+}
+
 static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stream, bool want_grad) {
   CallLists lists;
   if (check_call(plan, c, want_grad, lists)) return 1;
@@ -235,6 +274,7 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
   a.group = c->group;
   a.out_scale = c->out_scale;
   a.response_fn = c->response_fn;
+  if (a.trajectories && lists.n_rec > 0) encode_trajectory_map(a, lists.n_rec, c->dtype == 32 ? 4 : 8);
   int n_launched = 0;
   cudaError_t err = run_variant(*plan->variant, plan->prog, lists, a, c->dtype, want_grad, stream, &n_launched);
   g_launches += n_launched;
@@ -253,39 +293,74 @@ extern "C" int hgf_logp_grad(const hgf_plan_t* plan, const hgf_call_t* call, voi
 // host-buffer entry points: stage in, run, stage out
 // ---------------------------------------------------------------------------
 namespace {
-struct Staging {
+// Per-thread, per-device staging context of the *_host entry points: one non-blocking stream and one device
+// arena that only grows, so that a sampler calling hgf_logp_grad_host thousands of times pays for stream
+// creation and device allocation once (they cost more than the copies themselves for a 65 536-instance batch).
+struct HostContext {
+  int device = -1;
   cudaStream_t stream = nullptr;
-  std::vector<void*> device;
+  char* arena = nullptr;
+  size_t capacity = 0;
+  ~HostContext() { release(); }
+  void release() {
+    if (arena) cudaFree(arena);
+    if (stream) cudaStreamDestroy(stream);
+    arena = nullptr; stream = nullptr; capacity = 0; device = -1;
+  }
+  cudaError_t prepare(int dev, size_t bytes) {
+    cudaError_t e = cudaSetDevice(dev);
+    if (e != cudaSuccess) return e;
+    if (dev != device) { release(); device = dev; }
+    if (!stream) {
+      e = cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking);
+      if (e != cudaSuccess) return e;
+    }
+    if (bytes > capacity) {
+      if (arena) { cudaStreamSynchronize(stream); cudaFree(arena); arena = nullptr; capacity = 0; }
+      const size_t want = bytes + bytes / 4;
+      e = cudaMalloc(reinterpret_cast<void**>(&arena), want);
+      if (e != cudaSuccess) return e;
+      capacity = want;
+    }
+    return cudaSuccess;
+  }
+};
+thread_local HostContext g_host;
+
+constexpr size_t kAlign = 256;
+inline size_t aligned(size_t b) { return (b + kAlign - 1) / kAlign * kAlign; }
+
+struct Staging {
+  HostContext* ctx;
+  size_t offset = 0;
   struct Out { void* dev; void* host; size_t bytes; };
   std::vector<Out> outs;
   cudaError_t err = cudaSuccess;
-  const void* in(const void* host, size_t bytes) {
-    if (!host || bytes == 0 || err != cudaSuccess) return nullptr;
-    void* d = nullptr;
-    err = cudaMallocAsync(&d, bytes, stream);
-    if (err != cudaSuccess) return nullptr;
-    device.push_back(d);
-    err = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, stream);
+  void* take(size_t bytes) {
+    void* d = ctx->arena + offset;
+    offset += aligned(bytes);
     return d;
   }
-  void* out(void* host, size_t bytes, bool zero_from_host = false) {
+  const void* in(const void* host, size_t bytes) {
     if (!host || bytes == 0 || err != cudaSuccess) return nullptr;
-    void* d = nullptr;
-    err = cudaMallocAsync(&d, bytes, stream);
-    if (err != cudaSuccess) return nullptr;
-    device.push_back(d);
-    if (zero_from_host) err = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, stream);
+    void* d = take(bytes);
+    err = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, ctx->stream);
+    return d;
+  }
+  void* out(void* host, size_t bytes, bool init_from_host = false) {
+    if (!host || bytes == 0 || err != cudaSuccess) return nullptr;
+    void* d = take(bytes);
+    if (init_from_host) err = cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, ctx->stream);
     outs.push_back({d, host, bytes});
     return d;
   }
   void finish() {
     if (err == cudaSuccess)
       for (auto& o : outs) {
-        err = cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, stream);
+        err = cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, ctx->stream);
         if (err != cudaSuccess) break;
       }
-    for (void* d : device) cudaFreeAsync(d, stream);
-    cudaError_t e2 = cudaStreamSynchronize(stream);
+    cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
     if (err == cudaSuccess) err = e2;
   }
 };
@@ -294,8 +369,6 @@ struct Staging {
 static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, bool want_grad) {
   CallLists lists;
   if (check_call(plan, c, want_grad, lists)) return 1;
-  cudaError_t e = cudaSetDevice(device);
-  if (e != cudaSuccess) return fail("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
   const Program& p = plan->prog;
   const size_t w = c->dtype == 32 ? 4 : 8;
   const size_t N = static_cast<size_t>(c->n_instances), T = static_cast<size_t>(c->n_steps);
@@ -304,27 +377,38 @@ static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, boo
   int n_groups = 1;
   if (c->reduced && c->group)
     for (size_t i = 0; i < N; ++i) n_groups = c->group[i] + 1 > n_groups ? c->group[i] + 1 : n_groups;
+  // (pointer, bytes) of every staged array, in the order they are taken below
+  const size_t sz_in = n_in_series * T * p.n_fed * w, sz_obs = n_in_series * T * p.n_fed, sz_ts = T * w;
+  const size_t sz_attr = static_cast<size_t>(p.n_slots) * w, sz_par = static_cast<size_t>(c->n_params) * N * w;
+  const size_t sz_resp = n_resp_series * T * w, sz_group = N * sizeof(int32_t);
+  const size_t sz_traj = static_cast<size_t>(lists.n_rec) * T * N * w, sz_last = static_cast<size_t>(p.n_nodes) * NF * N * w;
+  const size_t sz_sum = N * w, sz_pw = T * N * w, sz_grad = sz_par, sz_red = static_cast<size_t>(n_groups) * w;
+  auto need = [](const void* ptr, size_t b) { return ptr && b ? aligned(b) : size_t(0); };
+  const size_t total = need(c->input_data, sz_in) + need(c->observed, sz_obs) + need(c->time_steps, sz_ts) + need(c->attributes, sz_attr) +
+                       need(c->params, sz_par) + need(c->response_inputs, sz_resp) + need(c->group, sz_group) + need(c->trajectories, sz_traj) +
+                       need(c->last_attributes, sz_last) + need(c->surprise_sum, sz_sum) + need(c->surprise_pointwise, sz_pw) +
+                       (want_grad ? need(c->gradient, sz_grad) : 0) + need(c->reduced, sz_red);
+  cudaError_t e = g_host.prepare(device, total);
+  if (e != cudaSuccess) return fail("host staging on device %d (%zu bytes): %s", device, total, cudaGetErrorString(e));
   Staging st;
-  e = cudaStreamCreateWithFlags(&st.stream, cudaStreamNonBlocking);
-  if (e != cudaSuccess) return fail("cudaStreamCreate: %s", cudaGetErrorString(e));
+  st.ctx = &g_host;
   hgf_call_t d = *c;
-  d.input_data = st.in(c->input_data, n_in_series * T * p.n_fed * w);
-  d.observed = static_cast<const uint8_t*>(st.in(c->observed, n_in_series * T * p.n_fed));
-  d.time_steps = st.in(c->time_steps, T * w);
-  d.attributes = st.in(c->attributes, static_cast<size_t>(p.n_slots) * w);
-  d.params = st.in(c->params, static_cast<size_t>(c->n_params) * N * w);
-  d.response_inputs = st.in(c->response_inputs, n_resp_series * T * w);
-  d.group = static_cast<const int32_t*>(st.in(c->group, N * sizeof(int32_t)));
-  d.trajectories = st.out(c->trajectories, static_cast<size_t>(lists.n_rec) * T * N * w);
-  d.last_attributes = st.out(c->last_attributes, static_cast<size_t>(p.n_nodes) * NF * N * w);
-  d.surprise_sum = st.out(c->surprise_sum, N * w);
-  d.surprise_pointwise = st.out(c->surprise_pointwise, T * N * w);
-  d.gradient = want_grad ? st.out(c->gradient, static_cast<size_t>(c->n_params) * N * w) : nullptr;
-  d.reduced = st.out(c->reduced, static_cast<size_t>(n_groups) * w, true);
+  d.input_data = st.in(c->input_data, sz_in);
+  d.observed = static_cast<const uint8_t*>(st.in(c->observed, sz_obs));
+  d.time_steps = st.in(c->time_steps, sz_ts);
+  d.attributes = st.in(c->attributes, sz_attr);
+  d.params = st.in(c->params, sz_par);
+  d.response_inputs = st.in(c->response_inputs, sz_resp);
+  d.group = static_cast<const int32_t*>(st.in(c->group, sz_group));
+  d.trajectories = st.out(c->trajectories, sz_traj);
+  d.last_attributes = st.out(c->last_attributes, sz_last);
+  d.surprise_sum = st.out(c->surprise_sum, sz_sum);
+  d.surprise_pointwise = st.out(c->surprise_pointwise, sz_pw);
+  d.gradient = want_grad ? st.out(c->gradient, sz_grad) : nullptr;
+  d.reduced = st.out(c->reduced, sz_red, true);
   int rc = 0;
-  if (st.err == cudaSuccess) rc = launch(plan, &d, st.stream, want_grad);
+  if (st.err == cudaSuccess) rc = launch(plan, &d, g_host.stream, want_grad);
   st.finish();
-  cudaStreamDestroy(st.stream);
   if (rc) return rc;
   if (st.err != cudaSuccess) return fail("host staging failed: %s", cudaGetErrorString(st.err));
   return 0;

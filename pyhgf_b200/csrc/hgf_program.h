@@ -117,6 +117,12 @@ struct ScanArgs {
   // expected_precision per node, + the *_vol twins of volatile nodes, in slot order) are recorded;
   // leaf r is stored in trajectory row popcount(mask below r)
   uint32_t rec_mask[4];
+  // Trajectory write-back through TMA (hgf_scan.cuh): when traj_rows > 0 each block stages the step's recorded
+  // leaves in shared memory as [traj_rows][SCAN_THREADS] and one thread issues a single 3-D tensor store
+  // (box = SCAN_THREADS instances x 1 step x traj_rows leaves) into trajectories[R][T][N]; traj_map is the
+  // CUtensorMap of that array (encoded per call by hgf_capi.cu).  traj_rows == 0: plain coalesced stores.
+  int traj_rows;
+  alignas(64) unsigned char traj_map[128];
 };
 
 }  // namespace hgf

@@ -22,11 +22,32 @@ constexpr int SCAN_THREADS = 64;
 template <class T, int PR> struct response_scalar { using type = Dual<base_t<T>, scalar_traits<T>::n_tangents + PR>; };
 template <class T, int PR> using response_scalar_t = typename response_scalar<T, PR>::type;
 
+#ifdef __CUDA_ARCH__
+// One TMA tensor store per block per step: the staged [rows][SCAN_THREADS] tile -> trajectories[0:rows][t][n0:n0+64]
+// (cp.async.bulk.tensor, bulk-group completion; instances past N are clipped by the tensor map's bounds).
+// Called by every thread of the block, in uniform control flow.
+template <class B> __device__ __forceinline__ void tma_store_step(const ScanArgs& args, B* stage, int t) {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // this thread's staged values -> visible to the async proxy
+  // the store of step t-1 must have finished reading its buffer before step t+1 overwrites it
+  if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const B* src = stage + static_cast<size_t>(t & 1) * args.traj_rows * SCAN_THREADS;
+    const unsigned smem = static_cast<unsigned>(__cvta_generic_to_shared(src));
+    const int c0 = static_cast<int>(blockIdx.x) * SCAN_THREADS;
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];"
+                 ::"l"(reinterpret_cast<unsigned long long>(args.traj_map)), "r"(c0), "r"(t), "r"(0), "r"(smem)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  }
+}
+#endif
+
 // One instance, all time steps.  Returns the summed surprise (with its tangents);
 // every per-instance output is stored here when `active`.
 template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT>
 HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallLists& lists, const ScanArgs& args, long long n,
-                                             bool active) {
+                                             bool active, base_t<T>* stage = nullptr) {
   using B = base_t<T>;
   using TR = response_scalar_t<T, PR>;
   constexpr int PF = scalar_traits<T>::n_tangents;
@@ -129,27 +150,48 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
       if (pointwise && active) pointwise[static_cast<long long>(t) * N + n] = pv(r);
       if (response_fn == RESP_TOTAL_GAUSSIAN && a.n_nodes() > 1 && x_isnan(HGF_S(1, F_MEAN))) node1_mean_nan = true;
     }
-    if (traj && active) {
+    if (traj && (active || stage)) {
+      // `stage` (TMA write-back): this thread's column of the block's [rows][SCAN_THREADS] staging tile for step t
+      // (double-buffered); otherwise a direct store, coalesced over the warp's instances
+      B* col = nullptr;
+#ifdef __CUDA_ARCH__
+      if (stage) col = stage + static_cast<size_t>(t & 1) * args.traj_rows * SCAN_THREADS + threadIdx.x;
+#endif
+      B* direct = traj + static_cast<long long>(t) * N + n;
+      const long long leaf_stride = static_cast<long long>(T_steps) * N;
       if constexpr (Topo::is_static) {
-        // static leaf set (see ScanArgs::rec_mask): warp-uniform predicates, coalesced stores
+        // static leaf set (see ScanArgs::rec_mask): warp-uniform predicates
         int leaf = 0, row = 0;
 #pragma unroll
         for (int node = 0; node < a.n_nodes(); ++node) {
 #pragma unroll
           for (int f = 0; f < 4; ++f, ++leaf)
-            if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) traj[(static_cast<long long>(row++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
+            if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) {
+              if (col) col[row * SCAN_THREADS] = pv(HGF_S(node, f)); else direct[row * leaf_stride] = pv(HGF_S(node, f));
+              ++row;
+            }
           if (a.node_type(node) == NODE_VOLATILE) {
 #pragma unroll
             for (int f = F_MEAN_VOL; f < F_MEAN_VOL + 4; ++f, ++leaf)
-              if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) traj[(static_cast<long long>(row++) * T_steps + t) * N + n] = pv(HGF_S(node, f));
+              if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) {
+                if (col) col[row * SCAN_THREADS] = pv(HGF_S(node, f)); else direct[row * leaf_stride] = pv(HGF_S(node, f));
+                ++row;
+              }
           }
         }
       } else {
-        for (int r = 0; r < lists.n_rec; ++r)
-          traj[(static_cast<long long>(r) * T_steps + t) * N + n] = pv(s[lists.rec_slot[r]]);
+        for (int r = 0; r < lists.n_rec; ++r) {
+          if (col) col[r * SCAN_THREADS] = pv(s[lists.rec_slot[r]]); else direct[r * leaf_stride] = pv(s[lists.rec_slot[r]]);
+        }
       }
+#ifdef __CUDA_ARCH__
+      if (stage) tma_store_step(args, stage, t);
+#endif
     }
   }
+#ifdef __CUDA_ARCH__
+  if (traj && stage && threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem outlives the last store
+#endif
 
   // response.py:87-89: total_gaussian_surprise is +inf everywhere if node 1's mean ever was NaN
   if (response_fn == RESP_TOTAL_GAUSSIAN && node1_mean_nan) total = TR(b_inf<B>());
@@ -213,7 +255,9 @@ scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLi
   long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool active = n < args.n_instances;
   if (!active) n = args.n_instances - 1;  // keep the warp whole for the shuffle reduction; stores are predicated
-  const auto total = scan_instance<T, Topo, NSLOTS, PR, UNIT_DT>(prog, lists, args, n, active);
+  extern __shared__ __align__(128) unsigned char hgf_stage[];
+  B* stage = args.traj_rows > 0 ? reinterpret_cast<B*>(hgf_stage) : nullptr;
+  const auto total = scan_instance<T, Topo, NSLOTS, PR, UNIT_DT>(prog, lists, args, n, active, stage);
   if (args.reduced) {
     const int g = args.group ? __ldg(args.group + n) : 0;
     reduce_into_groups<B>(static_cast<B*>(args.reduced), g, static_cast<B>(args.out_scale) * pv(total), active);

@@ -468,3 +468,33 @@ def test_config5_trajectories_layout(G, datasets):
             for k in nets.BELIEFS:
                 got = res.trajectories[(i, k)][n_i].double().cpu().numpy()
                 assert np.allclose(got, single.node_trajectories[i][k], rtol=RTOL_TRAJ, atol=1e-6), (n_i, i, k)
+
+
+@pytest.mark.parametrize("net_name,n", [("ghgf16", 260), ("ghgf16", 1000), ("binary3", 64), ("multi_child", 333)])
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+def test_tma_trajectory_writeback_is_bit_identical(G, datasets, net_name, n, dtype, monkeypatch):
+    """Trajectories written through shared-memory staging + one TMA tensor store per block-step equal, bit for
+    bit, those written with plain coalesced stores (HGF_NO_TMA=1) -- including the ragged last block (n not a
+    multiple of 64, clipped by the tensor map) and batches whose row stride is not 16-byte aligned (n = 333:
+    the library must fall back to plain stores by itself)."""
+    import torch
+
+    rng = np.random.default_rng(7)
+    if net_name == "binary3":
+        data, build, nodes = datasets["u"], nets.binary3, (1, 2)
+    elif net_name == "multi_child":  # interpreter path, two input columns
+        data, build, nodes = nets.ar1_series(200, n_series=2), nets.multi_child, (2, 3, 4, 5)
+    else:
+        data, build, nodes = nets.ar1_series(150), nets.ghgf16, tuple(range(4, 12))
+    params = {(i, "tonic_volatility"): rng.normal(-4, 0.5, n) for i in nodes}
+    record = [(i, k) for i in nodes for k in nets.BELIEFS]
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("HGF_NO_TMA", flag)
+        res = build(G.Network, dtype=dtype).batch(data, params, record=record)
+        torch.cuda.synchronize()
+        out[flag] = {k: res.trajectories[k].clone() for k in record}
+    for k in record:
+        a, b = out["0"][k], out["1"][k]
+        assert a.shape == (n, data.shape[0])
+        assert torch.equal(torch.nan_to_num(a, nan=123.0), torch.nan_to_num(b, nan=123.0)), k
