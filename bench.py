@@ -30,6 +30,10 @@ N_PARTICIPANTS, N_CHAINS, N_TRIALS, N_NODES = 1024, 64, 320, 3
 # algorithmic work of one 3-level binary step (forward), + inverse-temperature response
 MUFU_PER_STEP = 55 + 5
 MUFU_PEAK_PER_CLK_PER_SM, N_SM = 16, 148
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel on this workload, from the
+# `ncu --set full` capture summarised in profiles/r1_ncu_c4_logp_grad.txt (3.70 MB read, 0 B written: the
+# 1.05 MB of results stay in L2 until evicted).  A constant from a profile, not measured in this run.
+NCU_DRAM_BYTES_PER_LAUNCH = 3703808
 
 
 def synth_config4(rank: int, n_participants: int = N_PARTICIPANTS, n_chains: int = N_CHAINS, n_trials: int = N_TRIALS):
@@ -219,6 +223,7 @@ def run_gpu(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = os.environ.get("HGF_NCCL_DEBUG", "WARN")  # keep NCCL's banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()
 
@@ -230,15 +235,34 @@ def run_gpu(args):
     d_p = torch.from_numpy(params).to(dev)
     group = (torch.arange(n, device=dev, dtype=torch.int32) % N_CHAINS).contiguous()
     keys = [(1, "tonic_volatility"), (2, "tonic_volatility"), ("response_parameter", 0)]
-    res = net.batch(d_u, {k: d_p[i] for i, k in enumerate(keys)}, response_function=response.binary_softmax_inverse_temperature,
-                    response_function_inputs=d_y, input_group_size=N_CHAINS, response_group_size=N_CHAINS, gradient=True,
-                    group=group, n_groups=N_CHAINS, out_scale=-1.0)
+    # N > 1: the 64 per-chain sums are all-reduced INSIDE the kernel over NVLink peer memory (FusedReduce:
+    # multimem.red through the NVSwitch multicast mapping); HGF_BENCH_COLLECTIVE=nccl (or no symmetric memory on
+    # the box) falls back to one ncclAllReduce after the kernel
+    fused, collective = None, "none"
+    if world > 1:
+        collective = "ncclAllReduce of 64 per-chain sums after the kernel"
+        if os.environ.get("HGF_BENCH_COLLECTIVE", "fused") == "fused":
+            try:
+                from pyhgf_b200.distributed import FusedReduce
+
+                fused = FusedReduce(N_CHAINS, 32, dev)
+                collective = ("in-kernel all-reduce of 64 per-chain sums over NVLink peer memory (" +
+                              ("multimem.red, NVSwitch multicast" if fused.multicast_ptr else "per-peer red") + "), no NCCL call")
+            except Exception as exc:  # noqa: BLE001 - symmetric memory unavailable: keep NCCL
+                collective += f" (fused path unavailable: {type(exc).__name__})"
+
+    def evaluate(fr):
+        return net.batch(d_u, {k: d_p[i] for i, k in enumerate(keys)}, response_function=response.binary_softmax_inverse_temperature,
+                         response_function_inputs=d_y, input_group_size=N_CHAINS, response_group_size=N_CHAINS, gradient=True,
+                         group=group, n_groups=N_CHAINS, out_scale=-1.0, fused_reduce=fr)
+
+    res = evaluate(fused)
     torch.cuda.synchronize()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def step():
         res.relaunch()
-        if world > 1:
+        if world > 1 and fused is None:
             dist.all_reduce(res.reduced)  # the 64 per-chain sums: the path's only exchange
 
     for _ in range(max(args.warmup, 0)):
@@ -259,7 +283,7 @@ def run_gpu(args):
             starts[i].record()
             res.relaunch()
             mids[i].record()
-            if world > 1:
+            if world > 1 and fused is None:
                 dist.all_reduce(res.reduced)
             ends[i].record()
         torch.cuda.synchronize()
@@ -274,6 +298,15 @@ def run_gpu(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     step_ms = float(t.item())
+
+    collective_err = None
+    if world > 1:  # the reduced sums against a plain NCCL all-reduce of an un-fused launch (outside the timing)
+        got = res.reduced.clone()
+        ref = evaluate(None)
+        want = ref.reduced.clone()
+        dist.all_reduce(want)
+        torch.cuda.synchronize()
+        collective_err = float(((got - want).abs() / want.abs().clamp_min(1e-30)).max())
 
     e2e_dt, h2d, d2h, e2e_logp = e2e_leg(net, net.plan, u, y, params, args.steps, max(args.warmup, 3), local)
     same = np.allclose(e2e_logp, res.surprise.cpu().numpy(), rtol=1e-6, equal_nan=True)
@@ -305,12 +338,12 @@ def run_gpu(args):
             "config": {"workload": "config4: 3-level binary HGF logp+grad (omega_2, omega_3, inverse temperature), "
                                    f"{N_PARTICIPANTS} participants x {N_CHAINS} chains x {N_TRIALS} trials per GPU",
                        "instances_per_gpu": n, "trials": N_TRIALS, "nodes": N_NODES, "kernel": res.kernel_name,
-                       "l2": "flushed between timed iterations (256 MiB write)", "collective": "all-reduce of 64 per-chain sums" if world > 1 else "none"},
+                       "l2": "flushed between timed iterations (256 MiB write)", "collective": collective, "collective_max_rel_err_vs_nccl": collective_err},
             "logp_grad_evals_per_s": world * n * args.steps / (step_ms * 1e-3),
             "wall_ms_per_step": 1e3 * wall / args.steps,
             "kernel_ms": kern_ms,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": None, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                          "note": "the kernel is FP32/SFU-bound, not HBM-bound: see roofline_compute"},
             "roofline_compute": {"bound": "mufu", "achieved": mufu, "peak": mufu_peak, "unit": "op/s", "frac": mufu / mufu_peak,
                                  "note": f"algorithmic forward count {MUFU_PER_STEP} MUFU-class ops per instance-step (SURVEY 8d); "

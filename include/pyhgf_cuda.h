@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define HGF_ABI_VERSION 1
+#define HGF_ABI_VERSION 2
 
 /* number of scalar attribute fields per node, and their order (slot = node * HGF_N_FIELDS + field).
  * Names are the reference's attribute keys, pyhgf/model/add_nodes.py:65-85, 159-184, 330-340. */
@@ -107,6 +107,21 @@ typedef struct {
   void* reduced;                 /* [n_groups] += surprise_sum of the instances of each group; caller zeroes it */
   const int32_t* group;          /* [N] group (e.g. chain) of each instance, or NULL: everything into reduced[0] */
   double out_scale;
+  /* Fused cross-GPU reduction (optional; world_size <= 1: off).  One process per GPU; every rank allocates a
+   * workspace of hgf_fused_reduce_bytes() in memory that its peers can map (CUDA VMM / torch symmetric memory),
+   * zero-filled before the first launch, and passes all ranks' mappings.  The kernel then sums the per-group
+   * (per-chain) results of ALL ranks itself: the last block of each rank adds its G partial sums into every
+   * peer's workspace over NVLink (one multimem.red per value when a multicast mapping is given, else one red per
+   * peer), signals its peers and waits for theirs -- no NCCL call follows the kernel.  When the launch completes,
+   * workspace + hgf_fused_reduce_result_offset(n_groups, dtype, epoch) holds the all-reduced [G] sums; they stay
+   * valid until the launch after next.  `reduced` must be NULL; `epoch` counts the launches on this workspace
+   * (0, 1, 2, ...) and must be the same on every rank. */
+  int32_t n_groups;              /* G */
+  int32_t world_size;            /* W <= 8 */
+  int32_t rank;
+  uint32_t epoch;
+  void* const* peer_workspace;   /* HOST [W]: device addresses, in THIS process, of every rank's workspace */
+  void* multicast_workspace;     /* multicast address of the same workspace, or NULL */
 } hgf_call_t;
 
 int hgf_abi_version(void);
@@ -133,6 +148,10 @@ int hgf_logp_grad(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
 /* Same, with every data pointer in HOST memory (pageable or pinned); copies in, runs, copies out, synchronises. */
 int hgf_filter_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device);
 int hgf_logp_grad_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device);
+
+/* fused cross-GPU reduction workspace: size, and where the all-reduced [n_groups] sums of a launch are */
+int64_t hgf_fused_reduce_bytes(int32_t n_groups, int32_t dtype);
+int64_t hgf_fused_reduce_result_offset(int32_t n_groups, int32_t dtype, uint32_t epoch);
 
 /* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
 int64_t hgf_launch_count(void);

@@ -95,6 +95,12 @@ class Call(C.Structure):
         ("reduced", C.c_void_p),
         ("group", C.c_void_p),
         ("out_scale", C.c_double),
+        ("n_groups", C.c_int32),
+        ("world_size", C.c_int32),
+        ("rank", C.c_int32),
+        ("epoch", C.c_uint32),
+        ("peer_workspace", C.POINTER(C.c_void_p)),
+        ("multicast_workspace", C.c_void_p),
     ]
 
 
@@ -103,6 +109,7 @@ EXPORTS = (
     "hgf_abi_version", "hgf_last_error", "hgf_plan_create", "hgf_plan_destroy", "hgf_plan_n_slots",
     "hgf_plan_slot_coupling", "hgf_plan_slot_clipping", "hgf_plan_slot_response", "hgf_plan_kernel_name",
     "hgf_filter", "hgf_logp_grad", "hgf_filter_host", "hgf_logp_grad_host", "hgf_launch_count",
+    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset",
 )
 
 _lib = None
@@ -147,7 +154,11 @@ def lib() -> C.CDLL:
         f.argtypes = [C.c_void_p, C.POINTER(Call), C.c_int32]
         f.restype = C.c_int
     L.hgf_launch_count.restype = C.c_int64
-    if L.hgf_abi_version() != 1:
+    L.hgf_fused_reduce_bytes.argtypes = [C.c_int32, C.c_int32]
+    L.hgf_fused_reduce_bytes.restype = C.c_int64
+    L.hgf_fused_reduce_result_offset.argtypes = [C.c_int32, C.c_int32, C.c_uint32]
+    L.hgf_fused_reduce_result_offset.restype = C.c_int64
+    if L.hgf_abi_version() != 2:
         raise ImportError("libpyhgf_cuda.so ABI version mismatch; rebuild with `python -m pyhgf_b200.build --force`")
     _lib = L
     return L

@@ -43,6 +43,12 @@ extern "C" {
 int hgf_abi_version(void) { return HGF_ABI_VERSION; }
 const char* hgf_last_error(void) { return g_error.c_str(); }
 int64_t hgf_launch_count(void) { return g_launches.load(); }
+int64_t hgf_fused_reduce_bytes(int32_t n_groups, int32_t dtype) {
+  return (n_groups < 1 || (dtype != 32 && dtype != 64)) ? -1 : fused_bytes(n_groups, dtype / 8);
+}
+int64_t hgf_fused_reduce_result_offset(int32_t n_groups, int32_t dtype, uint32_t epoch) {
+  return (n_groups < 1 || (dtype != 32 && dtype != 64)) ? -1 : static_cast<int64_t>(epoch & 1u) * n_groups * (dtype / 8);
+}
 
 int hgf_plan_create(const hgf_topology_t* t, hgf_plan_t** out) {
   if (!t || !out) return fail("hgf_plan_create: null argument");
@@ -187,6 +193,14 @@ static int check_call(const hgf_plan_t* plan, const hgf_call_t* c, bool want_gra
     return fail("response function %d needs response_inputs", c->response_fn);
   if ((c->response_fn == RESP_FIRST_LEVEL_GAUSSIAN) && p.n_nodes < 2) return fail("first_level_gaussian_surprise needs a node 1");
   if (c->input_group_size < 0 || c->response_group_size < 0) return fail("negative group size");
+  if (c->world_size > 1) {
+    if (c->world_size > MAX_PEERS) return fail("world_size=%d; the fused reduction spans at most %d GPUs", c->world_size, MAX_PEERS);
+    if (c->rank < 0 || c->rank >= c->world_size) return fail("rank %d outside [0, %d)", c->rank, c->world_size);
+    if (!c->peer_workspace || c->n_groups < 1) return fail("fused reduction needs peer_workspace and n_groups >= 1");
+    for (int p = 0; p < c->world_size; ++p)
+      if (!c->peer_workspace[p]) return fail("peer_workspace[%d] is null", p);
+    if (c->reduced) return fail("fused reduction writes into the workspace: reduced must be null");
+  }
   if (want_grad && !c->gradient) return fail("hgf_logp_grad: gradient is null");
   if (want_grad && c->n_params < 1) return fail("hgf_logp_grad: no per-instance parameter to differentiate");
   if (!want_grad && c->gradient) return fail("hgf_filter: gradient must be null (use hgf_logp_grad)");
@@ -274,6 +288,14 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
   a.group = c->group;
   a.out_scale = c->out_scale;
   a.response_fn = c->response_fn;
+  if (c->world_size > 1) {
+    a.world = c->world_size;
+    a.rank = c->rank;
+    a.n_groups = c->n_groups;
+    a.epoch = c->epoch;
+    for (int p = 0; p < c->world_size; ++p) a.peer_ws[p] = c->peer_workspace[p];
+    a.mc_ws = c->multicast_workspace;
+  }
   if (a.trajectories && lists.n_rec > 0) encode_trajectory_map(a, lists.n_rec, c->dtype == 32 ? 4 : 8);
   int n_launched = 0;
   cudaError_t err = run_variant(*plan->variant, plan->prog, lists, a, c->dtype, want_grad, stream, &n_launched);

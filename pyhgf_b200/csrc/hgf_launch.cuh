@@ -19,11 +19,12 @@ cudaError_t launch_one(const Program& prog, const CallLists& lists, const ScanAr
     kernel<<<static_cast<unsigned>(blocks), SCAN_THREADS, smem, stream>>>(prog, lists, args);
     return cudaGetLastError();
   };
+  const bool rec = args.trajectories != nullptr;  // logp-only launches run a kernel without any recording code
   if constexpr (Topo::is_static) {
     if (!args.time_steps)  // dt = 1 folds away (and with it log dt and the per-step load)
-      return go(scan_kernel<T, Topo, NSLOTS, PR, true>);
+      return rec ? go(scan_kernel<T, Topo, NSLOTS, PR, true, true>) : go(scan_kernel<T, Topo, NSLOTS, PR, true, false>);
   }
-  return go(scan_kernel<T, Topo, NSLOTS, PR, false>);
+  return rec ? go(scan_kernel<T, Topo, NSLOTS, PR, false, true>) : go(scan_kernel<T, Topo, NSLOTS, PR, false, false>);
 }
 
 }  // namespace hgf

@@ -69,7 +69,7 @@ cudaError_t launch_scan(const Program& prog, const CallLists& lists_in, const Sc
     done_f += pf < remf ? pf : remf;
     done_r += pr;
     // later passes only add gradient columns
-    a.trajectories = nullptr; a.traj_rows = 0; a.last_attributes = nullptr; a.surprise_sum = nullptr; a.surprise_pointwise = nullptr; a.reduced = nullptr;
+    a.trajectories = nullptr; a.traj_rows = 0; a.last_attributes = nullptr; a.surprise_sum = nullptr; a.surprise_pointwise = nullptr; a.reduced = nullptr; a.world = 0;
   }
   return cudaSuccess;
 }

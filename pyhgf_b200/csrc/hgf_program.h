@@ -14,6 +14,7 @@ constexpr int MAX_INPUTS = 16;
 constexpr int MAX_RECORDS = 640;  // recorded (node, field) leaves
 constexpr int MAX_PARAMS = 16;    // batched (per-instance) parameters
 constexpr int N_RESP_PARAMS = 4;
+constexpr int MAX_PEERS = 8;      // GPUs of one box
 constexpr int INTERP_SLOTS = 768;  // attribute-vector capacity of the opcode interpreter
 
 // node_type codes: pyhgf/typing/typing.py:12-52
@@ -91,6 +92,16 @@ struct CallLists {
   uint16_t param_row[MAX_PARAMS];
 };
 
+// Workspace of the fused cross-GPU reduction, in scalars of width w: result[2][G] (double-buffered by epoch
+// parity), partial[G] (this rank's per-group sums), then two 32-bit words: block ticket counter, peer signal.
+#ifdef __CUDACC__
+#define HGF_PROGRAM_HD __host__ __device__
+#else
+#define HGF_PROGRAM_HD
+#endif
+HGF_PROGRAM_HD constexpr long long fused_ctl_offset(long long G, long long w) { return (3 * G * w + 15) / 16 * 16; }
+HGF_PROGRAM_HD constexpr long long fused_bytes(long long G, long long w) { return fused_ctl_offset(G, w) + 16; }
+
 // One launch's arguments (device pointers; see hgf_call_t in include/pyhgf_cuda.h).
 struct ScanArgs {
   long long n_instances;
@@ -122,6 +133,11 @@ struct ScanArgs {
   // (box = SCAN_THREADS instances x 1 step x traj_rows leaves) into trajectories[R][T][N]; traj_map is the
   // CUtensorMap of that array (encoded per call by hgf_capi.cu).  traj_rows == 0: plain coalesced stores.
   int traj_rows;
+  // fused cross-GPU reduction (hgf_call_t::peer_workspace, hgf_scan.cuh::fused_all_reduce); world <= 1: off
+  int world, rank, n_groups;
+  unsigned epoch;
+  void* peer_ws[MAX_PEERS];
+  void* mc_ws;
   alignas(64) unsigned char traj_map[128];
 };
 

@@ -12,6 +12,7 @@
 //   PR      extra tangent directions that exist only inside the response function
 //           (response-function parameters cannot influence the beliefs)
 //   UNIT_DT the call has no time_steps vector: dt = 1, log dt = 0 fold away
+//   REC     the call records trajectories (the logp-only kernels carry no recording code at all)
 #pragma once
 #include "hgf_ops.cuh"
 
@@ -45,7 +46,7 @@ template <class B> __device__ __forceinline__ void tma_store_step(const ScanArgs
 
 // One instance, all time steps.  Returns the summed surprise (with its tangents);
 // every per-instance output is stored here when `active`.
-template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT>
+template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT, bool REC = true>
 HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallLists& lists, const ScanArgs& args, long long n,
                                              bool active, base_t<T>* stage = nullptr) {
   using B = base_t<T>;
@@ -150,7 +151,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
       if (pointwise && active) pointwise[static_cast<long long>(t) * N + n] = pv(r);
       if (response_fn == RESP_TOTAL_GAUSSIAN && a.n_nodes() > 1 && x_isnan(HGF_S(1, F_MEAN))) node1_mean_nan = true;
     }
-    if (traj && (active || stage)) {
+    if (REC && traj && (active || stage)) {
       // `stage` (TMA write-back): this thread's column of the block's [rows][SCAN_THREADS] staging tile for step t
       // (double-buffered); otherwise a direct store, coalesced over the warp's instances
       B* col = nullptr;
@@ -190,7 +191,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
     }
   }
 #ifdef __CUDA_ARCH__
-  if (traj && stage && threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem outlives the last store
+  if (REC && traj && stage && threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem outlives the last store
 #endif
 
   // response.py:87-89: total_gaussian_surprise is +inf everywhere if node 1's mean ever was NaN
@@ -240,6 +241,73 @@ template <class B> __device__ __forceinline__ void reduce_into_groups(B* reduced
   }
 }
 
+// ---------------------------------------------------------------------------
+// Fused all-reduce of the per-group sums over NVLink peer memory (hgf_call_t::peer_workspace).
+// Every block has added its groups' sums into this rank's `partial`.  The LAST block of the grid (ticket
+// counter) then (1) zeroes the result buffer of the NEXT epoch, (2) adds each partial sum into the current
+// epoch's result buffer of EVERY rank -- one multimem.red through the NVSwitch multicast mapping, or one
+// system-scope red per peer -- (3) fences and raises every peer's signal word, and (4) waits until its own
+// signal shows that all W ranks have contributed.  Peers can only start adding epoch e+1 after seeing this
+// rank's epoch-e signal, which is sent after step (1): that is what makes the double buffer safe without any
+// host-side synchronisation.  Called by every thread of every block, in uniform control flow.
+template <class B> __device__ __forceinline__ void red_add_sys(B* p, B v) { atomicAdd_system(p, v); }
+__device__ __forceinline__ void multimem_red(float* p, float v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red(double* p, double v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+
+template <class B> __device__ __forceinline__ void fused_all_reduce(const ScanArgs& args) {
+  __shared__ int is_last;
+  const int G = args.n_groups, W = args.world;
+  B* ws = static_cast<B*>(args.peer_ws[args.rank]);
+  B* partial = ws + 2 * static_cast<size_t>(G);
+  unsigned* ctl = reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(ws) + fused_ctl_offset(G, sizeof(B)));
+  __syncthreads();  // this block's atomics into `partial` are issued
+  if (threadIdx.x == 0) {
+    __threadfence();
+    is_last = atomicAdd(ctl, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const unsigned e = args.epoch;
+  B* next = ws + static_cast<size_t>((e + 1) & 1u) * G;
+  for (int g = threadIdx.x; g < G; g += blockDim.x) next[g] = B(0);
+  const size_t cur = static_cast<size_t>(e & 1u) * G;
+  for (int g = threadIdx.x; g < G; g += blockDim.x) {
+    const B v = __ldcg(partial + g);
+    partial[g] = B(0);  // ready for the next launch
+    if (args.mc_ws) {
+      multimem_red(static_cast<B*>(args.mc_ws) + cur + g, v);
+    } else {
+      for (int p = 0; p < W; ++p) red_add_sys(static_cast<B*>(args.peer_ws[p]) + cur + g, v);
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *ctl = 0u;  // ticket counter, for the next launch
+    for (int p = 0; p < W; ++p) {
+      unsigned* peer_ctl = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(args.peer_ws[p]) + fused_ctl_offset(G, sizeof(B)));
+      atomicAdd_system(peer_ctl + 1, 1u);
+    }
+    const unsigned want = static_cast<unsigned>(W) * (e + 1u);
+    const long long t0 = clock64();
+    while (true) {
+      unsigned seen;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(ctl + 1) : "memory");
+      if (static_cast<int>(seen - want) >= 0) break;
+      if (clock64() - t0 > 20000000000LL) {  // ~10 s: a peer never arrived; poison the result instead of hanging the GPU
+        for (int g = 0; g < G; ++g) ws[cur + g] = b_nan<B>();
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
 // Occupancy: BASELINE config 4 gives each GPU 65 536 instances = 13.8 warps per SM; the float32 register-
 // resident kernels are bounded to 7 resident 64-thread blocks (<= 144 registers) so that the whole batch
 // is co-resident in one wave instead of 1.7 (a second, mostly empty wave costs ~40 %).
@@ -248,7 +316,7 @@ template <class T, class Topo> constexpr int scan_min_blocks() {
   return (Topo::is_static && sizeof(base_t<T>) == 4 && Topo::kNodes <= 4) ? 7 : 1;
 }
 
-template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT>
+template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT, bool REC>
 __global__ void __launch_bounds__(SCAN_THREADS, scan_min_blocks<T, Topo>())
 scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLists lists, const __grid_constant__ ScanArgs args) {
   using B = base_t<T>;
@@ -256,9 +324,14 @@ scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLi
   const bool active = n < args.n_instances;
   if (!active) n = args.n_instances - 1;  // keep the warp whole for the shuffle reduction; stores are predicated
   extern __shared__ __align__(128) unsigned char hgf_stage[];
-  B* stage = args.traj_rows > 0 ? reinterpret_cast<B*>(hgf_stage) : nullptr;
-  const auto total = scan_instance<T, Topo, NSLOTS, PR, UNIT_DT>(prog, lists, args, n, active, stage);
-  if (args.reduced) {
+  B* stage = (REC && args.traj_rows > 0) ? reinterpret_cast<B*>(hgf_stage) : nullptr;
+  const auto total = scan_instance<T, Topo, NSLOTS, PR, UNIT_DT, REC>(prog, lists, args, n, active, stage);
+  if (args.world > 1) {
+    const int g = args.group ? __ldg(args.group + n) : 0;
+    B* partial = static_cast<B*>(args.peer_ws[args.rank]) + 2 * static_cast<size_t>(args.n_groups);
+    reduce_into_groups<B>(partial, g, static_cast<B>(args.out_scale) * pv(total), active);
+    fused_all_reduce<B>(args);
+  } else if (args.reduced) {
     const int g = args.group ? __ldg(args.group + n) : 0;
     reduce_into_groups<B>(static_cast<B*>(args.reduced), g, static_cast<B>(args.out_scale) * pv(total), active);
   }

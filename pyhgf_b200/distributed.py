@@ -51,6 +51,73 @@ def all_reduce_sums(tensors: Sequence[torch.Tensor], group: Optional[dist.Proces
         off += t.numel()
 
 
+class FusedReduce:
+    """Workspace of the IN-KERNEL all-reduce of the per-group (per-chain) sums (``hgf_call_t::peer_workspace``).
+
+    Each rank allocates ``hgf_fused_reduce_bytes`` of symmetric memory (CUDA VMM, mapped into every peer by
+    ``torch.distributed._symmetric_memory``); the kernel's last block adds the rank's sums into every peer's copy
+    over NVLink (one ``multimem.red`` per value through the NVSwitch multicast mapping when the driver offers one),
+    signals the peers and waits for theirs, so that when the launch completes ``result()`` holds the sums over
+    ALL ranks -- there is no NCCL call on the path.  Pass it to ``Network.batch(..., fused_reduce=...)``; every
+    rank must launch the same number of times (the epoch counter is part of the protocol).
+    """
+
+    def __init__(self, n_groups: int, bits: int = 32, device=None, group: Optional[dist.ProcessGroup] = None,
+                 multicast: bool = True):
+        import ctypes as C
+
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from . import _lib
+
+        L = _lib.lib()
+        group = dist.group.WORLD if group is None else group
+        self.n_groups, self.bits = int(n_groups), int(bits)
+        self.world_size, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world_size > 8:
+            raise ValueError("the fused reduction spans the GPUs of one box (<= 8)")
+        nbytes = int(L.hgf_fused_reduce_bytes(self.n_groups, self.bits))
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        try:
+            self.buffer = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        except RuntimeError:  # older torch: the group must be enabled first
+            symm_mem.enable_symm_mem_for_group(group.group_name)
+            self.buffer = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.buffer.zero_()
+        self.handle = symm_mem.rendezvous(self.buffer, group.group_name)
+        self.peer_ptrs = (C.c_void_p * self.world_size)(*[int(p) for p in self.handle.buffer_ptrs])
+        mc = 0
+        if multicast:
+            try:
+                mc = int(self.handle.multicast_ptr or 0)
+            except (RuntimeError, AttributeError):
+                mc = 0
+        self.multicast_ptr = mc
+        self.epoch = 0
+        self._L = L
+        torch.cuda.synchronize(device)
+        dist.barrier(group)  # every rank's workspace is zeroed before anyone's first launch
+
+    def attach(self, call) -> int:
+        """Fill the fused-reduction fields of an ``hgf_call_t`` for the next launch; returns its epoch."""
+        import ctypes as C
+
+        e = self.epoch
+        self.epoch += 1
+        call.n_groups, call.world_size, call.rank, call.epoch = self.n_groups, self.world_size, self.rank, e & 0xFFFFFFFF
+        call.peer_workspace = C.cast(self.peer_ptrs, C.POINTER(C.c_void_p))
+        call.multicast_workspace = self.multicast_ptr or None
+        call.reduced = None
+        return e
+
+    def result(self, epoch: Optional[int] = None) -> torch.Tensor:
+        """The all-reduced ``[n_groups]`` sums of launch ``epoch`` (default: the last one); valid until the launch after next."""
+        e = self.epoch - 1 if epoch is None else epoch
+        off = int(self._L.hgf_fused_reduce_result_offset(self.n_groups, self.bits, e & 0xFFFFFFFF))
+        w = self.bits // 8
+        return self.buffer[off:off + self.n_groups * w].view(torch.float32 if self.bits == 32 else torch.float64)
+
+
 class ShardedLogp:
     """``HGFDistribution`` over the ranks of a process group.
 

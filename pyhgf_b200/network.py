@@ -122,9 +122,14 @@ class BatchResult:
         in HBM; a sampler or a benchmark overwrites the parameter tensors in place between calls).
         Host cost: one C call."""
         s = torch.cuda.current_stream(self._device) if stream is None else stream
-        if self.reduced is not None:
+        fused = getattr(self, "_fused", None)
+        if fused is not None:
+            fused.attach(self._call)  # next epoch; the all-reduced sums land in the workspace
+        elif self.reduced is not None:
             self.reduced.zero_()
         _lib.check(self._fn(self._plan.handle, C.byref(self._call), C.c_void_p(s.cuda_stream)))
+        if fused is not None:
+            self.reduced = fused.result()
         return self
 
     @property
@@ -422,7 +427,7 @@ class Network:
     def _launch(self, *, values, observed, time_steps, input_group_size, n_instances, params: dict,
                 response_fn: int, response_inputs, response_group_size, response_parameters, record_slots,
                 want_last, want_sum, want_pointwise, want_grad, group, n_groups, out_scale=1.0, stream=None,
-                attributes=None):
+                attributes=None, fused_reduce=None):
         L = _lib.lib()
         dev = values.device
         dt = _torch_dtype(self.bits)
@@ -507,8 +512,13 @@ class Network:
             grad = torch.empty((P, N), device=dev, dtype=dt)
             call.gradient = grad.data_ptr()
         if n_groups:
-            res.reduced = torch.zeros(n_groups, device=dev, dtype=dt)
-            call.reduced = res.reduced.data_ptr()
+            if fused_reduce is not None:
+                if fused_reduce.n_groups != n_groups or fused_reduce.bits != self.bits:
+                    raise ValueError("fused_reduce was built for another n_groups / dtype")
+                fused_reduce.attach(call)
+            else:
+                res.reduced = torch.zeros(n_groups, device=dev, dtype=dt)
+                call.reduced = res.reduced.data_ptr()
             if group is not None:
                 g = torch.as_tensor(group).to(device=dev, dtype=torch.int32).contiguous()
                 keep.append(g)
@@ -525,6 +535,9 @@ class Network:
         res._call, res._fn, res._plan, res._keep, res._device = call, fn, plan, (keep, slots, rec), dev
         res._traj = traj
         res._last = last
+        res._fused = fused_reduce if n_groups else None
+        if res._fused is not None:
+            res.reduced = fused_reduce.result()
         if grad is not None:
             res.gradient = {k: grad[i] for i, k in enumerate(keys)}
             res._grad = grad
@@ -626,7 +639,8 @@ class Network:
               response_function_inputs=None, response_function_parameters=None, time_steps=None, observed=None,
               n_instances: Optional[int] = None, input_group_size: int = 0, response_group_size: int = 0,
               record: Sequence[tuple] = (), last_attributes: bool = False, pointwise: bool = False,
-              gradient: bool = False, group=None, n_groups: int = 0, out_scale: float = 1.0, stream=None) -> BatchResult:
+              gradient: bool = False, group=None, n_groups: int = 0, out_scale: float = 1.0, stream=None,
+              fused_reduce=None) -> BatchResult:
         """Run N independent instances of this network in one launch.
 
         What the reference writes as ``jax.vmap(lambda p: Network()...input_data(u).surprise(f).sum())(params)``
@@ -641,6 +655,8 @@ class Network:
         record : ``[(node, attribute), ...]`` leaves to record at every step -> ``result.trajectories``.
         gradient : also return d(surprise)/d(parameters) (``hgf_logp_grad``).
         group / n_groups : sum ``out_scale * surprise`` of the instances of each group (e.g. chain) on the device.
+        fused_reduce : a ``pyhgf_b200.distributed.FusedReduce``: the group sums are all-reduced over the ranks
+            by the kernel itself (NVLink peer memory); ``result.reduced`` then holds the sums over all ranks.
         """
         parameters = dict(parameters or {})
         if self.scan_fn is None:
@@ -676,7 +692,8 @@ class Network:
                                  response_inputs=ri, response_group_size=response_group_size,
                                  response_parameters=response_function_parameters, record_slots=rec_slots,
                                  want_last=last_attributes, want_sum=name is not None, want_pointwise=pointwise and name is not None,
-                                 want_grad=gradient, group=group, n_groups=n_groups, out_scale=out_scale, stream=stream)
+                                 want_grad=gradient, group=group, n_groups=n_groups, out_scale=out_scale, stream=stream,
+                                 fused_reduce=fused_reduce)
         if rec_slots:
             res.trajectories = {tuple(k): res._traj[i].t() for i, k in enumerate(record)}
         if last_attributes:
