@@ -498,3 +498,22 @@ def test_tma_trajectory_writeback_is_bit_identical(G, datasets, net_name, n, dty
         a, b = out["0"][k], out["1"][k]
         assert a.shape == (n, data.shape[0])
         assert torch.equal(torch.nan_to_num(a, nan=123.0), torch.nan_to_num(b, nan=123.0)), k
+
+
+def test_fused_all_reduce_two_gpus():
+    """The in-kernel all-reduce over NVLink peer memory against NCCL (tools/test_fused_reduce.py under torchrun):
+    needs two GPUs, so it is skipped on the single-GPU box."""
+    import os
+    import subprocess
+    import sys
+
+    import torch
+
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29533", os.path.join(root, "tools", "test_fused_reduce.py")], capture_output=True, text=True,
+                       timeout=600, cwd=root)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert '"max_rel_err_vs_nccl"' in r.stdout
