@@ -544,6 +544,31 @@ class Network:
         return self
 
     # -- Network.surprise -- network.py:986-1022 ----------------------------------
+    def to_pandas(self):
+        """pyhgf/utils/to_pandas.py:14-136 (state nodes of type 1, 2, 6): sufficient statistics, per-node surprise
+        (binary_surprise / gaussian_surprise of each node's `mean` under its own prediction) and their row sum."""
+        import pandas as pd
+
+        nt, bits = self.node_trajectories, 32 if self.dtype == np.float32 else 64
+        ts = np.asarray(nt[-1]["time_step"])
+        cols = {"time_steps": ts, "time": np.cumsum(ts)}
+        for types in ((1, 2), (6,)):
+            for i, e in enumerate(self.edges):
+                if e.node_type in types:
+                    for var, v in nt[i].items():
+                        if ("mean" in var) or ("precision" in var) or ("observed" in var):
+                            cols[f"x_{i}_{var}"] = np.asarray(v)
+        for i, e in enumerate(self.edges):
+            if e.node_type == 1:
+                cols[f"x_{i}_surprise"] = np.array([binary_surprise(x, m, bits) for x, m in zip(nt[i]["mean"], nt[i]["expected_mean"])])
+        for i, e in enumerate(self.edges):
+            if e.node_type in (2, 6):
+                cols[f"x_{i}_surprise"] = np.array([gaussian_surprise(x, m, p, bits) for x, m, p in
+                                                    zip(nt[i]["mean"], nt[i]["expected_mean"], nt[i]["expected_precision"])])
+        df = pd.DataFrame(cols)
+        df["total_surprise"] = df.iloc[:, df.columns.str.contains("_surprise")].sum(axis=1, min_count=1)
+        return df
+
     def surprise(self, response_function, response_function_inputs=(), response_function_parameters=None):
         return response_function(
             hgf=self, response_function_inputs=response_function_inputs,

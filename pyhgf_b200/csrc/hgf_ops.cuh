@@ -183,9 +183,10 @@ template <class T, class A> HGF_D void predict_continuous(const A& a, T* s, cons
     pi_cond = B(1) / (variance + omega);
     pi_marg = pi_cond;
   } else {
-    const T var_parents = value_parent_variance(a, s, st, node);
     pi_cond = B(1) / (variance + omega);
-    pi_marg = B(1) / (variance + omega + var_parents);
+    // without value parents the Laplace term is exactly 0 and the marginal precision IS the conditional one
+    // (same bits: x + 0 = x); skipping it saves a reciprocal per node per step
+    pi_marg = a.n_vp(node) == 0 ? pi_cond : B(1) / (variance + omega + value_parent_variance(a, s, st, node));
   }
   HGF_S(node, F_EFFECTIVE_PRECISION) = omega * pi_marg;
   if (a.n_vc(node) == 0 && a.n_volc(node) == 0 && a.n_volp(node) == 0) {  // :345-354
@@ -217,9 +218,10 @@ template <class T, class A> HGF_D void predict_volatile(const A& a, T* s, const 
     pi_cond = B(1) / (variance + omega);
     pi_marg = pi_cond;
   } else {
-    const T var_parents = value_parent_variance(a, s, st, node);
     pi_cond = B(1) / (variance + omega);
-    pi_marg = B(1) / (variance + omega + var_parents);
+    // without value parents the Laplace term is exactly 0 and the marginal precision IS the conditional one
+    // (same bits: x + 0 = x); skipping it saves a reciprocal per node per step
+    pi_marg = a.n_vp(node) == 0 ? pi_cond : B(1) / (variance + omega + value_parent_variance(a, s, st, node));
   }
   HGF_S(node, F_EXPECTED_MEAN) = predicted_mean(a, s, st, node, true);
   if (a.n_vc(node) == 0 && a.n_volc(node) == 0 && a.n_volp(node) == 0) {  // :288-301

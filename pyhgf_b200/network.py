@@ -612,6 +612,39 @@ class Network:
         return out
 
     # --------------------------------------------------------------- surprise
+    def to_pandas(self):
+        """Export the trajectories and the per-node surprise as a pandas data frame (pyhgf/utils/to_pandas.py:14-136,
+        state nodes of type 1, 2 and 6): ``time_steps``, ``time``, every ``x_{i}_{mean|precision|observed...}`` column,
+        ``x_{i}_surprise`` (``binary_surprise`` / ``gaussian_surprise`` of node i's ``mean`` under its own prediction,
+        pyhgf/math.py:209-297, evaluated in the network's dtype) and ``total_surprise``.  Host-side post-processing
+        of ``node_trajectories``, as in the reference."""
+        import pandas as pd
+
+        if self.node_trajectories is None:
+            raise ValueError("to_pandas needs recorded trajectories: call input_data(..., record_trajectories=True) first")
+        nt, ft = self.node_trajectories, _np_dtype(self.bits)
+        ts = np.asarray(nt[-1]["time_step"])
+        cols = {"time_steps": ts, "time": np.cumsum(ts)}
+        for types in ((1, 2), (6,)):
+            for i, e in enumerate(self.edges):
+                if e.node_type in types:
+                    for var, v in nt[i].items():
+                        if var != "temp" and v is not None and (("mean" in var) or ("precision" in var) or ("observed" in var)):
+                            cols[f"x_{i}_{var}"] = np.asarray(v)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            for i, e in enumerate(self.edges):
+                if e.node_type == 1:  # math.py:270-297
+                    x, m = np.asarray(nt[i]["mean"], dtype=ft), np.asarray(nt[i]["expected_mean"], dtype=ft)
+                    m = np.clip(m, ft(1e-6), ft(1.0) - ft(1e-6))
+                    cols[f"x_{i}_surprise"] = np.where(x != 0, -np.log(m), -np.log(ft(1.0) - m)).astype(ft)
+            for i, e in enumerate(self.edges):
+                if e.node_type in (2, 6):  # math.py:209-238
+                    x, m, p = (np.asarray(nt[i][k], dtype=ft) for k in ("mean", "expected_mean", "expected_precision"))
+                    cols[f"x_{i}_surprise"] = (ft(0.5) * (np.log(ft(2.0) * ft(np.pi)) - np.log(p) + p * np.square(x - m))).astype(ft)
+        df = pd.DataFrame(cols)
+        df["total_surprise"] = df.iloc[:, df.columns.str.contains("_surprise")].sum(axis=1, min_count=1)
+        return df
+
     def surprise(self, response_function: Callable, response_function_inputs=(), response_function_parameters=None):
         """Per-trial surprise under a response function (network.py:986-1022)."""
         return response_function(hgf=self, response_function_inputs=response_function_inputs,

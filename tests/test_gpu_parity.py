@@ -517,3 +517,21 @@ def test_fused_all_reduce_two_gpus():
                        timeout=600, cwd=root)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert '"max_rel_err_vs_nccl"' in r.stdout
+
+
+def test_to_pandas_matches_the_notebook_goldens_and_the_oracle(G, datasets):
+    """`Network.to_pandas()` on the CUDA trajectories: 1.1-Binary_HGF.ipynb cell 27, 1.3-Continuous_HGF.ipynb cell 16."""
+    g = nets.binary3(G.Network).input_data(datasets["u"])
+    o = nets.binary3(onet.Network).input_data(datasets["u"])
+    dg, do = g.to_pandas(), o.to_pandas()
+    assert list(dg.columns) == list(do.columns)
+    for col, gold in (("x_0_surprise", 206.60437), ("x_1_surprise", 291.26907), ("x_2_surprise", 238.23419)):
+        assert np.isclose(dg[col].sum(), gold, rtol=RTOL_SUM), (col, dg[col].sum())
+        assert np.allclose(dg[col], do[col], rtol=1e-4, atol=1e-5)
+    x = datasets["x"]
+    build = lambda cls: (cls().add_nodes(precision=1e4).add_nodes(precision=1e4, mean=x[0], tonic_volatility=-13.0, value_children=0)  # noqa: E731
+                         .add_nodes(precision=1e1, tonic_volatility=-2.0, volatility_children=1).input_data(x))
+    dg = build(G.Network).to_pandas()
+    for col, gold in (("x_0_surprise", -2071.4644), ("x_1_surprise", -2446.2734), ("x_2_surprise", 665.03186)):
+        assert np.isclose(dg[col].sum(), gold, rtol=RTOL_SUM), (col, dg[col].sum())
+    assert np.isclose(dg.total_surprise.sum(), -2071.4644 - 2446.2734 + 665.03186, rtol=RTOL_SUM)

@@ -411,3 +411,25 @@ def test_batch_matches_single(datasets):
         ref = single.surprise(first_level_binary_surprise)
         # batch sums in float32 inside the scan; the trajectory path sums float32 terms in float64
         assert np.isclose(s[n], ref.sum(), rtol=2e-6)
+
+
+# --------------------------------------------------------------------------- docs/source/notebooks goldens (to_pandas)
+def test_to_pandas_notebook_goldens(datasets):
+    """1.1-Binary_HGF.ipynb cell 27 and 1.3-Continuous_HGF.ipynb cell 16: per-node surprise sums of
+    `Network.to_pandas()` (pyhgf/utils/to_pandas.py:88-112)."""
+    net = (Network().add_nodes(kind="binary-state").add_nodes(value_children=0).add_nodes(volatility_children=1)
+           .input_data(datasets["u"]))
+    df = net.to_pandas()
+    assert close(df.x_0_surprise.sum(), 206.60437)
+    assert close(df.x_1_surprise.sum(), 291.26907)
+    assert close(df.x_2_surprise.sum(), 238.23419)
+    assert close(df.total_surprise.sum(), 206.60437 + 291.26907 + 238.23419)
+    x = datasets["x"]
+    net = (Network().add_nodes(precision=1e4)
+           .add_nodes(precision=1e4, mean=x[0], tonic_volatility=-13.0, value_children=0)
+           .add_nodes(precision=1e1, tonic_volatility=-2.0, volatility_children=1).input_data(x))
+    df = net.to_pandas()
+    assert close(df.x_0_surprise.sum(), -2071.4644)
+    assert close(df.x_1_surprise.sum(), -2446.2734)
+    assert close(df.x_2_surprise.sum(), 665.03186)
+    assert list(df.columns[:2]) == ["time_steps", "time"] and "x_1_expected_precision" in df.columns
