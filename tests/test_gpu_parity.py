@@ -535,3 +535,124 @@ def test_to_pandas_matches_the_notebook_goldens_and_the_oracle(G, datasets):
     for col, gold in (("x_0_surprise", -2071.4644), ("x_1_surprise", -2446.2734), ("x_2_surprise", 665.03186)):
         assert np.isclose(dg[col].sum(), gold, rtol=RTOL_SUM), (col, dg[col].sum())
     assert np.isclose(dg.total_surprise.sum(), -2071.4644 - 2446.2734 + 665.03186, rtol=RTOL_SUM)
+
+
+# ------------------------------------------------------------------ BASELINE configs at full size: size-independent properties
+def _config4(n_part=1024, n_chain=64, T=320, seed=0):
+    rng = np.random.default_rng(seed)
+    blocks = rng.integers(0, 2, size=(n_part, (T + 39) // 40))
+    p = np.where(np.repeat(blocks, 40, axis=1)[:, :T] == 1, 0.8, 0.2)
+    u = (rng.uniform(size=p.shape) < p).astype(np.float32)
+    y = (rng.uniform(size=p.shape) < 0.3 + 0.4 * p).astype(np.float32)
+    n = n_part * n_chain
+    params = np.stack([rng.uniform(-6, -3, n), rng.uniform(-6, -3, n), np.exp(rng.uniform(-0.3, 0.8, n))]).astype(np.float32)
+    return u, y, params
+
+
+def test_config4_full_size_properties(G, R):
+    """1 024 participants x 64 chains x 320 trials, logp + gradient in one launch (BASELINE config 4):
+    (i) the per-chain sums reduced on the device equal the sums of the per-instance logp; (ii) an instance's logp and
+    gradient do not depend on the batch around it (a 2-participant sub-batch reproduces them bit for bit);
+    (iii) the gradient wrt the inverse temperature is the derivative of logp (central difference in float64 on a
+    sample); (iv) a random sample matches the oracle."""
+    import torch
+
+    n_part, n_chain = 1024, 64
+    u, y, p = _config4(n_part, n_chain)
+    n = n_part * n_chain
+    keys = [(1, "tonic_volatility"), (2, "tonic_volatility"), ("response_parameter", 0)]
+    group = torch.arange(n, device="cuda", dtype=torch.int32) % n_chain
+
+    def run(u_, y_, p_, dtype="float32", **kw):
+        return nets.binary3(G.Network, dtype=dtype).batch(u_, {k: p_[i] for i, k in enumerate(keys)},
+                                                          response_function=R.binary_softmax_inverse_temperature, response_function_inputs=y_,
+                                                          input_group_size=n_chain, response_group_size=n_chain, gradient=True, out_scale=-1.0, **kw)
+
+    res = run(u, y, p, group=group, n_groups=n_chain)
+    logp = res.surprise  # out_scale = -1: log-probabilities
+    assert logp.shape == (n,) and torch.isfinite(logp).all()
+    want = logp.double().view(n_part, n_chain).sum(0)
+    assert torch.allclose(res.reduced.double(), want, rtol=2e-5)                      # (i) float32 atomics vs float64 sum
+    lo = 517
+    sub = run(u[lo:lo + 2], y[lo:lo + 2], p[:, lo * n_chain:(lo + 2) * n_chain])
+    assert torch.equal(sub.surprise, logp[lo * n_chain:(lo + 2) * n_chain])           # (ii)
+    for k in keys:
+        assert torch.equal(sub.gradient[k], res.gradient[k][lo * n_chain:(lo + 2) * n_chain])
+    sel = slice(lo * n_chain, lo * n_chain + 32)
+    p64 = p[:, sel].astype(np.float64)
+    h = 1e-6
+    up, dn = p64.copy(), p64.copy()
+    up[2] += h
+    dn[2] -= h
+    u1, y1 = u[lo:lo + 1], y[lo:lo + 1]
+    f = lambda q: run(u1, y1, q, dtype="float64").surprise.cpu().numpy()  # noqa: E731
+    fd = (f(up) - f(dn)) / (2 * h)
+    g64 = run(u1, y1, p64, dtype="float64").gradient[keys[2]].cpu().numpy()
+    assert np.allclose(g64, fd, rtol=1e-5, atol=1e-6)                                  # (iii)
+    g32 = res.gradient[keys[2]][sel].double().cpu().numpy()
+    assert np.median(np.abs(g32 - g64) / (np.abs(g64) + 1e-3 * np.abs(g64).max())) < 1e-4
+    idx = np.random.default_rng(3).choice(n, 256, replace=False)                      # (iv)
+    o = nets.binary3(onet.Network).create_belief_propagation_fn()
+    o64 = nets.binary3(onet.Network, dtype="float64").create_belief_propagation_fn()
+    slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
+    got = -logp[torch.as_tensor(idx, device="cuda")].double().cpu().numpy()
+    s32 = np.array([o.batch_surprise(u[i // n_chain], slots, p[:, [i]].astype(np.float64), "binary_softmax_inverse_temperature", resp_inputs=y[i // n_chain])[0] for i in idx])
+    s64 = np.array([o64.batch_surprise(u[i // n_chain], slots, p[:, [i]].astype(np.float64), "binary_softmax_inverse_temperature", resp_inputs=y[i // n_chain])[0] for i in idx])
+    well = np.abs(s32 / s64 - 1) <= 1e-5
+    assert well.mean() > 0.8
+    assert np.allclose(got[well], s32[well], rtol=RTOL_SUM)
+
+
+def test_config2_full_size_properties(G, R, datasets):
+    """65 536 tonic-volatility samples x 614 observations, 4-node continuous HGF (BASELINE config 2): deterministic,
+    batch-independent, and a random sample matches the oracle."""
+    import torch
+
+    x = datasets["x"]
+    n = 65536
+    rng = np.random.default_rng(0)
+    om = [np.clip(rng.normal(m, 1.0, n), m - 3, m + 3).astype(np.float32) for m in (-13.0, -2.0, -2.0)]
+    keys = [(i, "tonic_volatility") for i in (1, 2, 3)]
+    run = lambda cols: nets.continuous3(G.Network).batch(x, dict(zip(keys, cols)), response_function=R.first_level_gaussian_surprise).surprise  # noqa: E731
+    a, b = run(om), run(om)
+    assert torch.equal(torch.nan_to_num(a, nan=1.0, posinf=2.0), torch.nan_to_num(b, nan=1.0, posinf=2.0))
+    sl = slice(40000, 40100)
+    c = run([v[sl] for v in om])
+    assert torch.equal(torch.nan_to_num(a[sl], nan=1.0, posinf=2.0), torch.nan_to_num(c, nan=1.0, posinf=2.0))
+    idx = rng.choice(n, 300, replace=False)
+    o = nets.continuous3(onet.Network).create_belief_propagation_fn()
+    slots = [o.slot(i, "tonic_volatility") for i in (1, 2, 3)]
+    want = o.batch_surprise(x, slots, np.stack([v[idx] for v in om]).astype(np.float64), "first_level_gaussian_surprise")
+    got = a[torch.as_tensor(idx, device="cuda")].double().cpu().numpy()
+    fin = np.isfinite(want)
+    assert np.array_equal(fin, np.isfinite(got))
+    assert np.allclose(got[fin], want[fin], rtol=RTOL_SUM, atol=1e-2)
+
+
+def test_config5_full_size_properties(G):
+    """16-node gHGF, 32 768 instances (one GPU's share of config 5) x 400 steps with all 80 belief leaves recorded
+    through the TMA write-back: instances with equal parameters give equal trajectories wherever they sit in the batch,
+    `expected_mean` of an autoconnected node at step t equals its `mean` at step t-1, and precisions stay positive."""
+    import torch
+
+    T, n = 400, 32768
+    x = nets.ar1_series(T)
+    rng = np.random.default_rng(1)
+    base = {i: rng.normal(-4, 1.0, n).astype(np.float32) for i in range(4, 12)}
+    for v in base.values():
+        v[n - 37] = v[5]  # a twin of instance 5 in the ragged tail of another block
+    params = {(i, "tonic_volatility"): base[i] for i in range(4, 12)}
+    record = [(i, k) for i in range(16) for k in nets.BELIEFS + (("mean_vol", "expected_mean_vol", "precision_vol", "expected_precision_vol") if i >= 12 else ())]
+    assert len(record) == 80
+    res = nets.ghgf16(G.Network).batch(x, params, record=record)
+    for k in record:
+        tr = res.trajectories[k]
+        assert tr.shape == (n, T)
+        assert torch.equal(torch.nan_to_num(tr[5], nan=7.0), torch.nan_to_num(tr[n - 37], nan=7.0)), k
+    for node in (4, 5, 6, 7):  # value parents: lambda = 1, no drift, no value parents of their own ... except 12/13's coupling
+        pr = res.trajectories[(node, "precision")]
+        assert (pr[torch.isfinite(pr)] > 0).all()
+    for node in (8, 9, 10, 11):  # volatility parents: mu_hat(t) = mu(t-1)
+        m, mh = res.trajectories[(node, "mean")], res.trajectories[(node, "expected_mean")]
+        ok = torch.isfinite(m[:, :-1]) & torch.isfinite(mh[:, 1:])
+        assert torch.equal(m[:, :-1][ok], mh[:, 1:][ok])
