@@ -130,6 +130,13 @@ const char* hgf_last_error(void);
 int hgf_plan_create(const hgf_topology_t* topology, hgf_plan_t** out);
 void hgf_plan_destroy(hgf_plan_t* plan);
 
+/* Register a register-resident specialisation built on demand for a user topology: `path` is a shared object
+ * produced by pyhgf_b200/specialise.py (the generated topology accessor + the kernels instantiated for it,
+ * compiled for sm_100a with this library's own headers).  Plans created afterwards dispatch to it when their
+ * network answers every topology query the way the specialisation was generated; everything else keeps running
+ * through the opcode interpreter.  The object stays loaded for the life of the process. */
+int hgf_register_specialisation(const char* path);
+
 /* attribute-vector layout */
 int32_t hgf_plan_n_slots(const hgf_plan_t* plan);
 /* kind: 0 value_coupling_parents, 1 volatility_coupling_parents, 2 value_coupling_children,

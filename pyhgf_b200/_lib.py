@@ -109,7 +109,7 @@ EXPORTS = (
     "hgf_abi_version", "hgf_last_error", "hgf_plan_create", "hgf_plan_destroy", "hgf_plan_n_slots",
     "hgf_plan_slot_coupling", "hgf_plan_slot_clipping", "hgf_plan_slot_response", "hgf_plan_kernel_name",
     "hgf_filter", "hgf_logp_grad", "hgf_filter_host", "hgf_logp_grad_host", "hgf_launch_count",
-    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset",
+    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_register_specialisation",
 )
 
 _lib = None
@@ -154,6 +154,8 @@ def lib() -> C.CDLL:
         f.argtypes = [C.c_void_p, C.POINTER(Call), C.c_int32]
         f.restype = C.c_int
     L.hgf_launch_count.restype = C.c_int64
+    L.hgf_register_specialisation.argtypes = [C.c_char_p]
+    L.hgf_register_specialisation.restype = C.c_int
     L.hgf_fused_reduce_bytes.argtypes = [C.c_int32, C.c_int32]
     L.hgf_fused_reduce_bytes.restype = C.c_int64
     L.hgf_fused_reduce_result_offset.argtypes = [C.c_int32, C.c_int32, C.c_uint32]

@@ -112,11 +112,18 @@ def _switch(name, args, table, default=0):
 
 def generate_topology(name, spec) -> str:
     factory, vol_updates, mean_field, _, _ = spec
-    g = factory()
+    return generate_header(name, factory(), vol_updates, mean_field)
+
+
+def generate_header(name, g, vol_updates, mean_field, inputs=None) -> str:
+    """The ``Topo_<name>`` accessor of a network description ``g`` (anything with ``.edges``): the BASELINE
+    topologies above at build time, any user network on demand (pyhgf_b200/specialise.py)."""
     edges = g.edges
     n = len(edges)
     pred, upd = get_update_sequence(g, vol_updates, mean_field)
-    inputs = tuple(i for i, e in enumerate(edges) if e.value_children is None and e.volatility_children is None)
+    if inputs is None:
+        inputs = tuple(i for i, e in enumerate(edges) if e.value_children is None and e.volatility_children is None)
+    inputs = tuple(int(i) for i in inputs)
     # slot layout of hgf_plan_create (hgf_program.h); checked at run time by topo_matches
     counts = {k: [len(getattr(e, k) or ()) for e in edges] for k in ("value_parents", "volatility_parents", "value_children", "volatility_children")}
     off = {k: [sum(v[:i]) for i in range(n)] for k, v in counts.items()}
@@ -131,8 +138,10 @@ def generate_topology(name, spec) -> str:
     def fn_of(parent, child):
         e = edges[parent]
         k = e.value_children.index(child)
-        f = e.coupling_fn[k] if k < len(e.coupling_fn) else None
-        return _lib.COUPLING_FNS[f]
+        f = e.coupling_fn[k] if (e.coupling_fn is not None and k < len(e.coupling_fn)) else None
+        from .topology import resolve_coupling_fn
+
+        return resolve_coupling_fn(f)
 
     t = {k: {} for k in ("vp", "vp_fn", "volp", "vc", "vc_fn", "volc", "slot_cvp", "slot_cvolp", "slot_cvc", "slot_cvolc")}
     for i, e in enumerate(edges):

@@ -9,6 +9,8 @@
 #include <string>
 #include <vector>
 
+#include <dlfcn.h>
+
 #include <cuda.h>  // CUtensorMap (types only: the encoder is fetched with cudaGetDriverEntryPoint, no libcuda link)
 #include <cstdlib>
 
@@ -155,6 +157,19 @@ int hgf_plan_create(const hgf_topology_t* t, hgf_plan_t** out) {
 }
 
 void hgf_plan_destroy(hgf_plan_t* plan) { delete plan; }
+
+int hgf_register_specialisation(const char* path) {
+  if (!path) return fail("hgf_register_specialisation: null path");
+  void* so = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+  if (!so) return fail("hgf_register_specialisation: %s", dlerror());
+  using Getter = const void* (*)();
+  Getter get = reinterpret_cast<Getter>(dlsym(so, "hgf_specialisation_variant"));
+  auto abi = reinterpret_cast<int (*)()>(dlsym(so, "hgf_specialisation_abi"));
+  if (!get || !abi) return fail("hgf_register_specialisation: %s is not a pyhgf_b200 specialisation", path);
+  if (abi() != HGF_ABI_VERSION) return fail("hgf_register_specialisation: %s was built for ABI %d, this library is %d", path, abi(), HGF_ABI_VERSION);
+  register_variant(static_cast<const KernelVariant*>(get()));
+  return 0;
+}
 
 int32_t hgf_plan_n_slots(const hgf_plan_t* plan) { return plan ? plan->prog.n_slots : -1; }
 int32_t hgf_plan_slot_coupling(const hgf_plan_t* plan, int32_t kind, int32_t node, int32_t pos) {

@@ -23,6 +23,8 @@ extern const KernelVariant kInterpreterVariant;
 const KernelVariant* const* static_variants();
 
 const KernelVariant* select_variant(const Program& prog);
+// on-demand specialisations (hgf_register_specialisation): consulted before the built-in table
+void register_variant(const KernelVariant* v);
 
 inline cudaError_t run_variant(const KernelVariant& v, const Program& prog, const CallLists& lists, const ScanArgs& args, int dtype,
                                bool want_grad, cudaStream_t stream, int* n_launched) {

@@ -281,6 +281,23 @@ class Network:
         self.scan_fn = None
         self.update_sequence = None
 
+    def _invalidate_plan(self):
+        self._plan = None
+
+    def specialise(self, gradient_parameters: int = 0, response_parameter: bool = False, float64: bool = False,
+                   verbose: bool = False) -> str:
+        """Build (once per topology, cached on disk) and register register-resident kernels for THIS network's
+        topology, so that it does not run through the opcode interpreter (``pyhgf_b200/specialise.py``).  The plain
+        filter is always instantiated; ``gradient_parameters = k`` adds the logp+grad kernel for k filter parameters
+        per pass (<= 4), ``response_parameter`` the variant that also differentiates one response-function parameter.
+        Returns the kernel name the network's plans report afterwards."""
+        from . import specialise as sp
+
+        kernels = [(0, 0)]
+        if gradient_parameters or response_parameter:
+            kernels.append((min(int(gradient_parameters), 4), 1 if response_parameter else 0))
+        return sp.specialise(self, float32=() if float64 else kernels, float64=kernels if float64 else (), verbose=verbose)
+
     # ----------------------------------------------------------------- inputs
     @property
     def input_idxs(self) -> tuple:

@@ -656,3 +656,41 @@ def test_config5_full_size_properties(G):
         m, mh = res.trajectories[(node, "mean")], res.trajectories[(node, "expected_mean")]
         ok = torch.isfinite(m[:, :-1]) & torch.isfinite(mh[:, 1:])
         assert torch.equal(m[:, :-1][ok], mh[:, 1:][ok])
+
+
+@pytest.mark.parametrize("build", [nets.multi_child, nets.volatile2, nets.nonlinear], ids=lambda b: b.__name__)
+def test_on_demand_specialisation_matches_the_interpreter(G, R, build, monkeypatch):
+    """A user topology specialised on demand (register-resident kernels, pyhgf_b200/specialise.py) gives the
+    interpreter's trajectories, logp and gradients."""
+    import torch
+
+    n_in = len(build(G.Network).input_idxs)
+    x = nets.ar1_series(200, n_series=n_in)
+    x = x if n_in > 1 else x[:, 0]
+    n = 300
+    rng = np.random.default_rng(3)
+    cont = [i for i, e in enumerate(build(G.Network).edges) if e.node_type == 2 and (e.value_children or e.volatility_children)]
+    params = {(i, "tonic_volatility"): rng.normal(-4, 0.3, n) for i in cont[:2]} or {(1, "tonic_volatility_vol"): rng.normal(-4, 0.3, n)}
+    record = [(i, k) for i in range(len(build(G.Network).edges)) for k in nets.BELIEFS]
+    out = {}
+    for mode in ("interpreter", "specialised"):
+        net = build(G.Network)
+        if mode == "specialised":
+            name = net.specialise(gradient_parameters=len(params))
+            assert net.plan.kernel_name == name
+        else:
+            monkeypatch.setenv("HGF_FORCE_INTERPRETER", "1")
+            net.create_belief_propagation_fn()
+            assert net.plan.kernel_name == "interpreter"
+        res = net.batch(x, params, record=record, response_function=R.total_gaussian_surprise, gradient=True)
+        assert res.kernel_name == net.plan.kernel_name
+        torch.cuda.synchronize()
+        out[mode] = res
+        monkeypatch.delenv("HGF_FORCE_INTERPRETER", raising=False)
+    a, b = out["interpreter"], out["specialised"]
+    assert torch.allclose(a.surprise, b.surprise, rtol=1e-5, equal_nan=True)
+    for k in params:
+        scale = float(a.gradient[k].abs().max())
+        assert torch.allclose(a.gradient[k], b.gradient[k], rtol=1e-3, atol=1e-4 * scale, equal_nan=True), k
+    for k in record:
+        assert torch.allclose(a.trajectories[k], b.trajectories[k], rtol=RTOL_TRAJ, atol=1e-6, equal_nan=True), k

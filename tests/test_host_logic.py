@@ -146,3 +146,23 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in text and "from oracle" not in text and "liboracle" not in text, f
+
+
+def test_on_demand_specialisation_builds_and_is_selected(lib):
+    """pyhgf_b200/specialise.py: a topology without a built-in specialisation gets register-resident kernels
+    compiled on demand (nvcc cross-compiles here), registered through hgf_register_specialisation and selected by
+    hgf_plan_create for exactly that topology -- other networks keep their own kernels."""
+    from pyhgf_b200.network import Network
+
+    net = nets.tanh_coupling(Network)
+    net.create_belief_propagation_fn()
+    assert net.plan.kernel_name == "interpreter"
+    name = net.specialise()
+    assert name.startswith("specialised:")
+    assert net.plan.kernel_name == name
+    assert nets.tanh_coupling(Network).plan.kernel_name == name          # same topology, another instance
+    assert nets.volatile2(Network).plan.kernel_name == "interpreter"     # a different one is untouched
+    assert nets.binary3(Network).plan.kernel_name == "static:binary3"
+    assert net.specialise() == name                                      # cached: no rebuild
+    L = lib.lib()
+    assert L.hgf_register_specialisation(b"/nonexistent.so") != 0 and b"nonexistent" in L.hgf_last_error()
