@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define HGF_ABI_VERSION 2
+#define HGF_ABI_VERSION 3
 
 /* number of scalar attribute fields per node, and their order (slot = node * HGF_N_FIELDS + field).
  * Names are the reference's attribute keys, pyhgf/model/add_nodes.py:65-85, 159-184, 330-340. */
@@ -122,6 +122,14 @@ typedef struct {
   uint32_t epoch;
   void* const* peer_workspace;   /* HOST [W]: device addresses, in THIS process, of every rank's workspace */
   void* multicast_workspace;     /* multicast address of the same workspace, or NULL */
+  /* Generative mode (beliefs_propagation(observations="generative"), pyhgf/utils/beliefs_propagation.py:109-125,
+   * pyhgf/utils/sample.py:18-116): instead of reading input_data, every input node observes a draw from its own
+   * prediction -- Bernoulli(expected_mean) for binary nodes, Normal(expected_mean, 1/expected_precision) for
+   * continuous ones (sample_node_distribution.py:34-40) -- with observed = 1.  As in the reference, all input nodes
+   * of one step share one random draw.  The stream is Philox4x32-10 keyed by (seed, instance, step); instances are
+   * the reference's n_predictions.  input_data / observed are ignored; hgf_filter only. */
+  int32_t generative;
+  uint64_t seed;
 } hgf_call_t;
 
 int hgf_abi_version(void);

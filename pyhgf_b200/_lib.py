@@ -101,6 +101,8 @@ class Call(C.Structure):
         ("epoch", C.c_uint32),
         ("peer_workspace", C.POINTER(C.c_void_p)),
         ("multicast_workspace", C.c_void_p),
+        ("generative", C.c_int32),
+        ("seed", C.c_uint64),
     ]
 
 
@@ -160,7 +162,7 @@ def lib() -> C.CDLL:
     L.hgf_fused_reduce_bytes.restype = C.c_int64
     L.hgf_fused_reduce_result_offset.argtypes = [C.c_int32, C.c_int32, C.c_uint32]
     L.hgf_fused_reduce_result_offset.restype = C.c_int64
-    if L.hgf_abi_version() != 2:
+    if L.hgf_abi_version() != 3:
         raise ImportError("libpyhgf_cuda.so ABI version mismatch; rebuild with `python -m pyhgf_b200.build --force`")
     _lib = L
     return L

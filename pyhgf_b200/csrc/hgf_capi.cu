@@ -198,7 +198,9 @@ static int check_call(const hgf_plan_t* plan, const hgf_call_t* c, bool want_gra
   if (c->dtype != 32 && c->dtype != 64) return fail("dtype must be 32 or 64, got %d", c->dtype);
   if (c->n_instances < 0 || c->n_steps < 0) return fail("negative n_instances / n_steps");
   if (!c->attributes) return fail("attributes is null");
-  if (p.n_fed > 0 && c->n_steps > 0 && !c->input_data) return fail("input_data is null");
+  if (p.n_fed > 0 && c->n_steps > 0 && !c->input_data && !c->generative) return fail("input_data is null");
+  if (c->generative && want_grad) return fail("generative mode runs through hgf_filter only");
+  if (c->generative && !(c->trajectories && c->n_records > 0)) return fail("generative mode needs recorded trajectories (the rollouts are the output)");
   if (c->n_params < 0 || c->n_params > MAX_PARAMS) return fail("n_params=%d outside [0, %d]", c->n_params, MAX_PARAMS);
   if (c->n_params > 0 && (!c->param_slots || (!c->params && c->n_instances > 0))) return fail("params / param_slots is null");
   if (c->n_records < 0 || c->n_records > MAX_RECORDS) return fail("n_records=%d outside [0, %d]", c->n_records, MAX_RECORDS);
@@ -303,6 +305,8 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
   a.group = c->group;
   a.out_scale = c->out_scale;
   a.response_fn = c->response_fn;
+  a.generative = c->generative ? 1 : 0;
+  a.seed = c->seed;
   if (c->world_size > 1) {
     a.world = c->world_size;
     a.rank = c->rank;

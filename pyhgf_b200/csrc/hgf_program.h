@@ -133,6 +133,9 @@ struct ScanArgs {
   // (box = SCAN_THREADS instances x 1 step x traj_rows leaves) into trajectories[R][T][N]; traj_map is the
   // CUtensorMap of that array (encoded per call by hgf_capi.cu).  traj_rows == 0: plain coalesced stores.
   int traj_rows;
+  // generative mode (hgf_call_t::generative): observations are drawn from the input nodes' predictions
+  int generative;
+  unsigned long long seed;
   // fused cross-GPU reduction (hgf_call_t::peer_workspace, hgf_scan.cuh::fused_all_reduce); world <= 1: off
   int world, rank, n_groups;
   unsigned epoch;

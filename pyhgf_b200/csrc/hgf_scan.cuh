@@ -23,6 +23,41 @@ constexpr int SCAN_THREADS = 64;
 template <class T, int PR> struct response_scalar { using type = Dual<base_t<T>, scalar_traits<T>::n_tangents + PR>; };
 template <class T, int PR> using response_scalar_t = typename response_scalar<T, PR>::type;
 
+// Philox4x32-10 (Salmon et al. 2011): the counter-based stream of the generative mode.  One call gives the four
+// 32-bit words of counter (instance, step) under key `seed`.
+HGF_HD void philox4x32(unsigned long long seed, unsigned long long instance, unsigned step, unsigned out[4]) {
+  unsigned c0 = static_cast<unsigned>(instance), c1 = static_cast<unsigned>(instance >> 32), c2 = step, c3 = 0x48474600u;
+  unsigned k0 = static_cast<unsigned>(seed), k1 = static_cast<unsigned>(seed >> 32);
+#pragma unroll
+  for (int round = 0; round < 10; ++round) {
+    const unsigned long long p0 = 0xD2511F53ull * c0, p1 = 0xCD9E8D57ull * c2;
+    const unsigned n0 = static_cast<unsigned>(p1 >> 32) ^ c1 ^ k0, n1 = static_cast<unsigned>(p1);
+    const unsigned n2 = static_cast<unsigned>(p0 >> 32) ^ c3 ^ k1, n3 = static_cast<unsigned>(p0);
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// One uniform in (0, 1) and one standard normal (Box-Muller) per instance-step, in double so that float32 and
+// float64 launches see the same draws.
+struct UniformNormal { double u, z; };
+#ifdef __CUDACC__
+static __host__ __device__ __noinline__  // a cold call: keeps its double-precision log / cos out of the time loop's registers
+#else
+static inline
+#endif
+UniformNormal draw_uniform_normal(unsigned long long seed, unsigned long long instance, unsigned step) {
+  unsigned r[4];
+  philox4x32(seed, instance, step, r);
+  UniformNormal d;
+  d.u = (static_cast<double>(r[0]) + 0.5) * (1.0 / 4294967296.0);
+  const double u1 = (static_cast<double>(r[1]) + 0.5) * (1.0 / 4294967296.0);
+  const double u2 = (static_cast<double>(r[2]) + 0.5) * (1.0 / 4294967296.0);
+  d.z = ::sqrt(-2.0 * ::log(u1)) * ::cos(6.283185307179586 * u2);
+  return d;
+}
+
 #ifdef __CUDA_ARCH__
 // One TMA tensor store per block per step: the staged [rows][SCAN_THREADS] tile -> trajectories[0:rows][t][n0:n0+64]
 // (cp.async.bulk.tensor, bulk-group completion; instances past N are clipped by the tensor map's bounds).
@@ -132,11 +167,29 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
       for (int i = 0; i < a.n_pred(); ++i) apply_op(a, s, st, a.pred_op(i), a.pred_node(i));
     }
     // set_observation, pyhgf/updates/observation.py:10-38
+    if (REC && args.generative) {  // rollouts always record: only the recording kernels carry this branch
+      // observations = "generative" (beliefs_propagation.py:109-125): every input node observes a draw from its own
+      // prediction (sample_node_distribution.py:34-40); one draw per step shared by the input nodes, as the reference
+      // samples all of them with the same key
+      const UniformNormal draw = draw_uniform_normal(args.seed, static_cast<unsigned long long>(n), static_cast<unsigned>(t));
+      const double du = draw.u, dz = draw.z;
 #pragma unroll (Topo::kUnroll)
-    for (int k = 0; k < n_fed; ++k) {
-      const int node = a.input_idx(k);
-      HGF_S(node, F_MEAN) = T(HGF_LDG(u + static_cast<long long>(t) * n_fed + k));
-      HGF_S(node, F_OBSERVED) = T(obs ? static_cast<B>(HGF_LDG(obs + static_cast<long long>(t) * n_fed + k)) : B(1));
+      for (int k = 0; k < a.n_inputs(); ++k) {
+        const int node = a.input_idx(k);
+        const B mu = pv(HGF_S(node, F_EXPECTED_MEAN));
+        B value;
+        if (a.node_type(node) == NODE_BINARY) value = (static_cast<B>(du) < mu) ? B(1) : B(0);
+        else value = static_cast<B>(dz) * (B(1) / static_cast<B>(::sqrt(static_cast<double>(pv(HGF_S(node, F_EXPECTED_PRECISION)))))) + mu;
+        HGF_S(node, F_MEAN) = T(value);
+        HGF_S(node, F_OBSERVED) = T(B(1));
+      }
+    } else {
+#pragma unroll (Topo::kUnroll)
+      for (int k = 0; k < n_fed; ++k) {
+        const int node = a.input_idx(k);
+        HGF_S(node, F_MEAN) = T(HGF_LDG(u + static_cast<long long>(t) * n_fed + k));
+        HGF_S(node, F_OBSERVED) = T(obs ? static_cast<B>(HGF_LDG(obs + static_cast<long long>(t) * n_fed + k)) : B(1));
+      }
     }
     // prediction errors and posterior updates (children before parents)
     if constexpr (Topo::is_static) {

@@ -444,7 +444,7 @@ class Network:
     def _launch(self, *, values, observed, time_steps, input_group_size, n_instances, params: dict,
                 response_fn: int, response_inputs, response_group_size, response_parameters, record_slots,
                 want_last, want_sum, want_pointwise, want_grad, group, n_groups, out_scale=1.0, stream=None,
-                attributes=None, fused_reduce=None):
+                attributes=None, fused_reduce=None, generative_seed=None):
         L = _lib.lib()
         dev = values.device
         dt = _torch_dtype(self.bits)
@@ -541,6 +541,8 @@ class Network:
                 keep.append(g)
                 call.group = g.data_ptr()
         call.out_scale = float(out_scale)
+        if generative_seed is not None:
+            call.generative, call.seed = 1, int(generative_seed) & 0xFFFFFFFFFFFFFFFF
         s = torch.cuda.current_stream(dev) if stream is None else stream
         fn = L.hgf_logp_grad if want_grad else L.hgf_filter
         with torch.cuda.device(dev):
@@ -629,6 +631,40 @@ class Network:
         return out
 
     # --------------------------------------------------------------- surprise
+    def sample(self, time_steps, n_predictions: int = 1, rng_key=0) -> dict:
+        """Sample ``n_predictions`` rollouts forward in generative mode (pyhgf/utils/sample.py:18-116): starting from
+        ``last_attributes`` (or the initial attributes), at every step each input node observes a draw from its own
+        prediction and the beliefs are updated on it.  One thread per rollout; the random stream is an in-kernel
+        Philox4x32-10 keyed by ``(rng_key, rollout, step)`` -- not JAX's threefry, so draws differ from the
+        reference's while their distribution is the same.  Returns ``{node: {field: tensor[n_predictions, T]}}``."""
+        if self.scan_fn is None:
+            self.create_belief_propagation_fn()
+        dev = self.device
+        ts = np.atleast_1d(np.asarray(time_steps, dtype=np.float64))
+        T, n_in = int(ts.size), len(self.input_idxs)
+        plan = self._get_plan(n_in)
+        start = self.last_attributes if getattr(self, "last_attributes", None) is not None else self.attributes
+        record = list(range(self.n_nodes * _lib.N_FIELDS))
+        dummy = torch.zeros((1, T, n_in), device=dev, dtype=_torch_dtype(self.bits))  # ignored by the kernel
+        res, plan = self._launch(values=dummy, observed=None, time_steps=ts, input_group_size=0, n_instances=int(n_predictions),
+                                 params={}, response_fn=0, response_inputs=None, response_group_size=0, response_parameters=None,
+                                 record_slots=record, want_last=False, want_sum=False, want_pointwise=False, want_grad=False,
+                                 group=None, n_groups=0, attributes=start, generative_seed=int(rng_key))
+        out = {}
+        for i in range(self.n_nodes):
+            a, d, temp = self.attributes[i], {}, {}
+            for k, name in enumerate(_lib.FIELDS):
+                col = res._traj[i * _lib.N_FIELDS + k].t()
+                if name.startswith("temp."):
+                    if name[5:] in a.get("temp", {}):
+                        temp[name[5:]] = col
+                elif name in a:
+                    d[name] = col
+            d["temp"] = temp
+            out[i] = d
+        out[-1] = {"time_step": torch.as_tensor(ts, device=dev).expand(int(n_predictions), T)}
+        return out
+
     def to_pandas(self):
         """Export the trajectories and the per-node surprise as a pandas data frame (pyhgf/utils/to_pandas.py:14-136,
         state nodes of type 1, 2 and 6): ``time_steps``, ``time``, every ``x_{i}_{mean|precision|observed...}`` column,

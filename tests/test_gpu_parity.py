@@ -694,3 +694,43 @@ def test_on_demand_specialisation_matches_the_interpreter(G, R, build, monkeypat
         assert torch.allclose(a.gradient[k], b.gradient[k], rtol=1e-3, atol=1e-4 * scale, equal_nan=True), k
     for k in record:
         assert torch.allclose(a.trajectories[k], b.trajectories[k], rtol=RTOL_TRAJ, atol=1e-6, equal_nan=True), k
+
+
+def test_generative_rollouts(G, datasets):
+    """`Network.sample` (pyhgf/utils/sample.py:18-116): in-kernel draws from the input nodes' predictions.
+    The random stream is Philox, not JAX's threefry, so the check is (i) the draws have the predicted distribution,
+    (ii) a rollout is exactly the filter run on its own samples (fed to the oracle as external observations),
+    (iii) same key -> same rollouts, another key -> different ones, (iv) rollouts start from `last_attributes`."""
+    import torch
+
+    n, T = 8192, 40
+    g = nets.binary3(G.Network)
+    pred = g.sample(time_steps=np.ones(T), n_predictions=n, rng_key=7)
+    u = pred[0]["mean"]
+    assert u.shape == (n, T) and bool(((u == 0) | (u == 1)).all())
+    mu0 = pred[0]["expected_mean"][:, 0]
+    assert torch.allclose(mu0, torch.full_like(mu0, 0.5))                      # default prior: sigmoid(0)
+    assert abs(float(u[:, 0].mean()) - 0.5) < 4 * 0.5 / n ** 0.5               # (i) Bernoulli(0.5)
+    # calibration over all steps: E[u - mu_hat] = 0, Var = E[mu_hat (1 - mu_hat)]
+    resid = (u - pred[0]["expected_mean"]).double()
+    assert abs(float(resid.mean())) < 4 * 0.5 / (n * T) ** 0.5
+    for i in (0, 4097, n - 1):                                                  # (ii)
+        o = nets.binary3(onet.Network).input_data(u[i].cpu().numpy().astype(float))
+        for node in (1, 2):
+            for k in nets.BELIEFS:
+                got = pred[node][k][i].double().cpu().numpy()
+                assert np.allclose(got, o.node_trajectories[node][k], rtol=RTOL_TRAJ, atol=1e-6), (i, node, k)
+    again = g.sample(time_steps=np.ones(T), n_predictions=n, rng_key=7)        # (iii)
+    other = g.sample(time_steps=np.ones(T), n_predictions=n, rng_key=8)
+    assert torch.equal(again[0]["mean"], u) and not torch.equal(other[0]["mean"], u)
+
+    # continuous input: standardised residuals of the draws are N(0, 1)
+    c = nets.continuous2(G.Network).input_data(datasets["x"][:100])            # (iv) start from the filtered state
+    pred = c.sample(time_steps=np.ones(20), n_predictions=n, rng_key=1)
+    x, m, p = (pred[0][k].double() for k in ("mean", "expected_mean", "expected_precision"))
+    zed = (x - m) * p.sqrt()
+    assert abs(float(zed.mean())) < 4 / (n * 20) ** 0.5
+    assert abs(float(zed.var()) - 1.0) < 0.05
+    assert abs(float((zed.abs() < 1.96).double().mean()) - 0.95) < 0.01
+    want = float(c.last_attributes[1]["mean"])                                  # lambda = 1, no drift: mu_hat(first step) = last mean
+    assert torch.allclose(pred[1]["expected_mean"][:, 0].double(), torch.full((n,), want, dtype=torch.float64, device="cuda"), rtol=1e-6)
