@@ -305,9 +305,22 @@ template <class T> HGF_D bool x_isfinite(const T& a) { return b_isfinite(pv(a));
 template <class T> HGF_D bool x_isnan(const T& a) { return b_isnan(pv(a)); }
 
 // jax.nn.sigmoid == lax.logistic == 1 / (1 + exp(-x))
-template <class T> HGF_D T x_sigmoid(const T& x) {
-  using B = base_t<T>;
-  return B(1) / (B(1) + x_exp(-x));
+HGF_D float x_sigmoid(float x) { return b_div(1.0f, 1.0f + b_exp(-x)); }
+HGF_D double x_sigmoid(double x) { return 1.0 / (1.0 + b_exp(-x)); }
+template <class B, int P> HGF_D Dual<B, P> x_sigmoid(const Dual<B, P>& x) {
+  // primal exactly as above; tangent in closed form, s (1 - s) dx, instead of differentiating exp and the division
+  Dual<B, P> r;
+#ifdef HGF_SFU_MATH
+  r.v = b_rcp(B(1) + b_exp(-x.v));
+#else
+  r.v = b_div(B(1), B(1) + b_exp(-x.v));
+#endif
+  if constexpr (P > 0) {
+    const B c = r.v * (B(1) - r.v);
+#pragma unroll
+    for (int i = 0; i < P; ++i) r.d[i] = c * x.d[i];
+  }
+  return r;
 }
 
 // jnp.logaddexp(a, b) = max + log1p(exp(-|a - b|)); NaN delta -> a + b
@@ -324,7 +337,12 @@ template <class B, int P> HGF_D Dual<B, P> x_logaddexp(const Dual<B, P>& a, cons
   // JVP of jnp.logaddexp: t1 * exp(x1 - out) + t2 * exp(x2 - out)
   Dual<B, P> r; r.v = b_logaddexp<B>(a.v, b.v);
   if constexpr (P > 0) {
-    const B wa = b_exp(a.v - r.v), wb = b_exp(b.v - r.v);
+    // the weights exp(x1 - out), exp(x2 - out) sum to one: w(larger) = 1 / (1 + exp(-|x1 - x2|)), w(smaller) = 1 - it
+    // (one reciprocal instead of two exponentials); a NaN anywhere gives NaN weights, as the JVP's would be
+    const B e = b_exp(-b_abs(a.v - b.v));
+    const B w_hi = b_rcp(B(1) + e), w_lo = B(1) - w_hi;
+    const bool a_hi = a.v >= b.v;
+    const B wa = a_hi ? w_hi : w_lo, wb = a_hi ? w_lo : w_hi;
 #pragma unroll
     for (int i = 0; i < P; ++i) r.d[i] = b_fma(a.d[i], wa, b.d[i] * wb);
   }
