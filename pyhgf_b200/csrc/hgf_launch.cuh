@@ -19,12 +19,24 @@ cudaError_t launch_one(const Program& prog, const CallLists& lists, const ScanAr
     kernel<<<static_cast<unsigned>(blocks), SCAN_THREADS, smem, stream>>>(prog, lists, args);
     return cudaGetLastError();
   };
-  const bool rec = args.trajectories != nullptr;  // logp-only launches run a kernel without any recording code
-  if constexpr (Topo::is_static) {
-    if (!args.time_steps)  // dt = 1 folds away (and with it log dt and the per-step load)
-      return rec ? go(scan_kernel<T, Topo, NSLOTS, PR, true, true>) : go(scan_kernel<T, Topo, NSLOTS, PR, true, false>);
+  // Recording kernels (REC) exist for the plain filter only: logp-only and gradient launches run kernels without any
+  // recording code, and a gradient call that also records trajectories gets them from an extra plain-filter pass
+  // (launch_scan).  That halves the number of gradient kernels to compile.
+  constexpr bool kPlain = scalar_traits<T>::n_tangents == 0 && PR == 0;
+  const bool rec = args.trajectories != nullptr;
+  if constexpr (!kPlain) {
+    if (rec) return cudaErrorInvalidValue;
+    if constexpr (Topo::is_static) {
+      if (!args.time_steps) return go(scan_kernel<T, Topo, NSLOTS, PR, true, false>);
+    }
+    return go(scan_kernel<T, Topo, NSLOTS, PR, false, false>);
+  } else {
+    if constexpr (Topo::is_static) {
+      if (!args.time_steps)  // dt = 1 folds away (and with it log dt and the per-step load)
+        return rec ? go(scan_kernel<T, Topo, NSLOTS, PR, true, true>) : go(scan_kernel<T, Topo, NSLOTS, PR, true, false>);
+    }
+    return rec ? go(scan_kernel<T, Topo, NSLOTS, PR, false, true>) : go(scan_kernel<T, Topo, NSLOTS, PR, false, false>);
   }
-  return rec ? go(scan_kernel<T, Topo, NSLOTS, PR, false, true>) : go(scan_kernel<T, Topo, NSLOTS, PR, false, false>);
 }
 
 }  // namespace hgf

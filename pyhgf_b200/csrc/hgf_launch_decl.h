@@ -47,6 +47,18 @@ cudaError_t launch_scan(const Program& prog, const CallLists& lists_in, const Sc
     ++*n_launched;
     return launch_variant<B, Topo, NSLOTS, MASK>(0, 0, prog, lists, a, stream);
   }
+  if (a.trajectories || a.last_attributes) {
+    // trajectories / final attributes of a gradient call: one plain-filter pass (the recording kernels carry no tangents)
+    if ((MASK & 1u) == 0) return cudaErrorNotSupported;
+    ScanArgs f = a;
+    f.surprise_sum = nullptr; f.surprise_pointwise = nullptr; f.gradient = nullptr; f.reduced = nullptr; f.world = 0; f.response_fn = RESP_NONE;
+    CallLists fl = lists;
+    fl.n_filter = fl.n_params;
+    const cudaError_t err = launch_variant<B, Topo, NSLOTS, MASK>(0, 0, prog, fl, f, stream);
+    ++*n_launched;
+    if (err != cudaSuccess) return err;
+    a.trajectories = nullptr; a.traj_rows = 0; a.last_attributes = nullptr;
+  }
   const int F = lists.n_filter, R = lists.n_params - lists.n_filter;
   int done_f = 0, done_r = 0;
   while (done_f < F || done_r < R) {
