@@ -280,13 +280,14 @@ static bool encode_trajectory_map(ScanArgs& a, int n_rec, int width) {
   return true;
 }
 
-static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stream, bool want_grad) {
+static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stream, bool want_grad, long long ld = 0) {
   CallLists lists;
   if (check_call(plan, c, want_grad, lists)) return 1;
   if (c->n_instances == 0) return 0;
   ScanArgs a;
   std::memset(&a, 0, sizeof a);
   a.n_instances = c->n_instances;
+  a.ld = ld > 0 ? ld : c->n_instances;
   a.n_steps = c->n_steps;
   a.input_group_size = c->input_group_size;
   a.response_group_size = c->response_group_size;
@@ -337,15 +338,22 @@ namespace {
 // Per-thread, per-device staging context of the *_host entry points: one non-blocking stream and one device
 // arena that only grows, so that a sampler calling hgf_logp_grad_host thousands of times pays for stream
 // creation and device allocation once (they cost more than the copies themselves for a 65 536-instance batch).
+constexpr int kHostChunks = 4;
 struct HostContext {
   int device = -1;
   cudaStream_t stream = nullptr;
+  cudaStream_t side[kHostChunks - 1] = {};  // chunk pipeline of the *_host entry points
+  cudaEvent_t shared_ready = nullptr, chunk_done[kHostChunks - 1] = {};
   char* arena = nullptr;
   size_t capacity = 0;
   ~HostContext() { release(); }
   void release() {
     if (arena) cudaFree(arena);
     if (stream) cudaStreamDestroy(stream);
+    for (auto& s : side) { if (s) cudaStreamDestroy(s); s = nullptr; }
+    for (auto& e : chunk_done) { if (e) cudaEventDestroy(e); e = nullptr; }
+    if (shared_ready) cudaEventDestroy(shared_ready);
+    shared_ready = nullptr;
     arena = nullptr; stream = nullptr; capacity = 0; device = -1;
   }
   cudaError_t prepare(int dev, size_t bytes) {
@@ -355,6 +363,11 @@ struct HostContext {
     if (!stream) {
       e = cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking);
       if (e != cudaSuccess) return e;
+      for (auto& s : side)
+        if ((e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)) != cudaSuccess) return e;
+      for (auto& ev : chunk_done)
+        if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
+      if ((e = cudaEventCreateWithFlags(&shared_ready, cudaEventDisableTiming)) != cudaSuccess) return e;
     }
     if (bytes > capacity) {
       if (arena) { cudaStreamSynchronize(stream); cudaFree(arena); arena = nullptr; capacity = 0; }
@@ -407,6 +420,103 @@ struct Staging {
 };
 }  // namespace
 
+// Large logp(+grad) batches: the instance range is cut into kHostChunks slices (whole series groups, multiples of
+// the block size), each with its own stream: slice k+1's host->device copies and slice k-1's device->host copies run
+// under slice k's kernel.  The device arrays keep the full [.][N] layout (row stride = N: ScanArgs::ld), so a slice is
+// a pointer offset.  Returns -1 when the call is not eligible (then the one-shot path below runs), else the result.
+static int run_host_chunked(const hgf_plan_t* plan, const hgf_call_t* c, bool want_grad, int n_groups) {
+  const char* env = std::getenv("HGF_HOST_CHUNKS");
+  if (env && env[0] == '0') return -1;
+  const Program& p = plan->prog;
+  const long long N = c->n_instances;
+  if (N < 32768 || c->trajectories || c->surprise_pointwise || c->last_attributes || c->world_size > 1 || c->generative) return -1;
+  if (!c->surprise_sum && !c->gradient) return -1;
+  auto lcm = [](long long a, long long b) { long long x = a, y = b; while (y) { long long t = x % y; x = y; y = t; } return a / x * b; };
+  long long unit = 64;
+  if (c->input_group_size > 0) unit = lcm(unit, c->input_group_size);
+  if (c->response_group_size > 0) unit = lcm(unit, c->response_group_size);
+  const long long per = ((N + kHostChunks - 1) / kHostChunks + unit - 1) / unit * unit;
+  if (per <= 0 || per >= N) return -1;
+  const size_t w = c->dtype == 32 ? 4 : 8, T = static_cast<size_t>(c->n_steps), F = static_cast<size_t>(p.n_fed), P = static_cast<size_t>(c->n_params);
+  const size_t in_series = c->input_group_size > 0 ? (N + c->input_group_size - 1) / c->input_group_size : 1;
+  const size_t resp_series = c->response_group_size > 0 ? (N + c->response_group_size - 1) / c->response_group_size : 1;
+  HostContext& h = g_host;
+  size_t off = 0;
+  auto take = [&](const void* host, size_t bytes) -> char* {
+    if (!host || !bytes) return nullptr;
+    char* d = h.arena + off;
+    off += aligned(bytes);
+    return d;
+  };
+  char* d_in = take(c->input_data, in_series * T * F * w);
+  char* d_obs = take(c->observed, in_series * T * F);
+  char* d_ts = take(c->time_steps, T * w);
+  char* d_attr = take(c->attributes, static_cast<size_t>(p.n_slots) * w);
+  char* d_par = take(c->params, P * N * w);
+  char* d_resp = take(c->response_inputs, resp_series * T * w);
+  char* d_group = take(c->group, N * sizeof(int32_t));
+  char* d_sum = take(c->surprise_sum, N * w);
+  char* d_grad = want_grad ? take(c->gradient, P * N * w) : nullptr;
+  char* d_red = take(c->reduced, static_cast<size_t>(n_groups) * w);
+  if (off > h.capacity) return -1;  // (prepare() sized the arena with the same terms; defensive)
+  cudaError_t err = cudaSuccess;
+  auto ok = [&](cudaError_t e) { if (err == cudaSuccess) err = e; };
+  auto h2d = [&](char* dst, const void* src, size_t bytes, cudaStream_t s) { if (dst && bytes) ok(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s)); };
+  h2d(d_ts, c->time_steps, T * w, h.stream);
+  h2d(d_attr, c->attributes, static_cast<size_t>(p.n_slots) * w, h.stream);
+  h2d(d_red, c->reduced, static_cast<size_t>(n_groups) * w, h.stream);
+  if (in_series == 1) { h2d(d_in, c->input_data, T * F * w, h.stream); h2d(d_obs, c->observed, T * F, h.stream); }
+  if (resp_series == 1) h2d(d_resp, c->response_inputs, T * w, h.stream);
+  ok(cudaEventRecord(h.shared_ready, h.stream));
+  int rc = 0, k = 0;
+  for (long long n0 = 0; n0 < N && rc == 0 && err == cudaSuccess; n0 += per, ++k) {
+    const long long nc = (n0 + per < N) ? per : N - n0;
+    cudaStream_t s = k == 0 ? h.stream : h.side[k - 1];
+    if (k > 0) ok(cudaStreamWaitEvent(s, h.shared_ready, 0));
+    hgf_call_t d = *c;
+    d.n_instances = nc;
+    if (in_series > 1) {
+      const size_t g0 = n0 / c->input_group_size, g1 = (n0 + nc + c->input_group_size - 1) / c->input_group_size;
+      h2d(d_in + g0 * T * F * w, static_cast<const char*>(c->input_data) + g0 * T * F * w, (g1 - g0) * T * F * w, s);
+      if (d_obs) h2d(d_obs + g0 * T * F, c->observed + g0 * T * F, (g1 - g0) * T * F, s);
+      d.input_data = d_in + g0 * T * F * w;
+      d.observed = d_obs ? reinterpret_cast<const uint8_t*>(d_obs + g0 * T * F) : nullptr;
+    } else {
+      d.input_data = d_in;
+      d.observed = reinterpret_cast<const uint8_t*>(d_obs);
+    }
+    if (resp_series > 1) {
+      const size_t g0 = n0 / c->response_group_size, g1 = (n0 + nc + c->response_group_size - 1) / c->response_group_size;
+      h2d(d_resp + g0 * T * w, static_cast<const char*>(c->response_inputs) + g0 * T * w, (g1 - g0) * T * w, s);
+      d.response_inputs = d_resp + g0 * T * w;
+    } else {
+      d.response_inputs = d_resp;
+    }
+    if (d_par) ok(cudaMemcpy2DAsync(d_par + n0 * w, N * w, static_cast<const char*>(c->params) + n0 * w, N * w, nc * w, P, cudaMemcpyHostToDevice, s));
+    if (d_group) h2d(d_group + n0 * sizeof(int32_t), c->group + n0, nc * sizeof(int32_t), s);
+    d.time_steps = d_ts;
+    d.attributes = d_attr;
+    d.params = d_par ? d_par + n0 * w : nullptr;
+    d.group = d_group ? reinterpret_cast<const int32_t*>(d_group + n0 * sizeof(int32_t)) : nullptr;
+    d.surprise_sum = d_sum ? d_sum + n0 * w : nullptr;
+    d.gradient = d_grad ? d_grad + n0 * w : nullptr;
+    d.reduced = d_red;
+    if (err == cudaSuccess) rc = launch(plan, &d, s, want_grad, N);
+    if (rc == 0) {
+      if (d_sum) ok(cudaMemcpyAsync(static_cast<char*>(c->surprise_sum) + n0 * w, d_sum + n0 * w, nc * w, cudaMemcpyDeviceToHost, s));
+      if (d_grad) ok(cudaMemcpy2DAsync(static_cast<char*>(c->gradient) + n0 * w, N * w, d_grad + n0 * w, N * w, nc * w, P, cudaMemcpyDeviceToHost, s));
+    }
+    if (k > 0) { ok(cudaEventRecord(h.chunk_done[k - 1], s)); ok(cudaStreamWaitEvent(h.stream, h.chunk_done[k - 1], 0)); }
+  }
+  if (rc == 0 && err == cudaSuccess && d_red) ok(cudaMemcpyAsync(c->reduced, d_red, static_cast<size_t>(n_groups) * w, cudaMemcpyDeviceToHost, h.stream));
+  const cudaError_t e2 = cudaStreamSynchronize(h.stream);
+  for (auto& s : h.side) cudaStreamSynchronize(s);
+  if (rc) return rc;
+  ok(e2);
+  if (err != cudaSuccess) return fail("host staging (chunked) failed: %s", cudaGetErrorString(err));
+  return 0;
+}
+
 static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, bool want_grad) {
   CallLists lists;
   if (check_call(plan, c, want_grad, lists)) return 1;
@@ -431,6 +541,7 @@ static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, boo
                        (want_grad ? need(c->gradient, sz_grad) : 0) + need(c->reduced, sz_red);
   cudaError_t e = g_host.prepare(device, total);
   if (e != cudaSuccess) return fail("host staging on device %d (%zu bytes): %s", device, total, cudaGetErrorString(e));
+  if (int rc = run_host_chunked(plan, c, want_grad, n_groups); rc >= 0) return rc;
   Staging st;
   st.ctx = &g_host;
   hgf_call_t d = *c;

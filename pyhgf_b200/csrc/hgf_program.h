@@ -105,6 +105,7 @@ HGF_PROGRAM_HD constexpr long long fused_bytes(long long G, long long w) { retur
 // One launch's arguments (device pointers; see hgf_call_t in include/pyhgf_cuda.h).
 struct ScanArgs {
   long long n_instances;
+  long long ld;  // leading dimension (row stride, in scalars) of params / gradient / pointwise / trajectories / last_attributes
   int n_steps;
   long long input_group_size, response_group_size;
   const void* input_data;

@@ -88,7 +88,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
   using TR = response_scalar_t<T, PR>;
   constexpr int PF = scalar_traits<T>::n_tangents;
   const Topo a(prog);
-  const long long N = args.n_instances;
+  const long long N = args.ld;  // row stride of every [.][N] array (== n_instances unless the launch covers a slice of a batch)
 
   // ---- initial attributes: shared vector + this instance's parameters ----
   T s[NSLOTS];

@@ -734,3 +734,43 @@ def test_generative_rollouts(G, datasets):
     assert abs(float((zed.abs() < 1.96).double().mean()) - 0.95) < 0.01
     want = float(c.last_attributes[1]["mean"])                                  # lambda = 1, no drift: mu_hat(first step) = last mean
     assert torch.allclose(pred[1]["expected_mean"][:, 0].double(), torch.full((n,), want, dtype=torch.float64, device="cuda"), rtol=1e-6)
+
+
+@pytest.mark.parametrize("n_part,n_chain,shared", [(800, 50, False), (1, 40000, True), (1024, 64, False)])
+def test_host_entry_point_chunk_pipeline(G, n_part, n_chain, shared, monkeypatch):
+    """hgf_logp_grad_host on a large batch: the chunked copy/compute pipeline (4 slices of whole series groups on 4
+    streams, ScanArgs::ld row strides) returns exactly what the one-shot path (HGF_HOST_CHUNKS=0) returns, for grouped
+    series whose group size does not divide the block size, and for one shared series."""
+    from pyhgf_b200 import _lib
+
+    rng = np.random.default_rng(2)
+    T = 96
+    n = n_part * n_chain
+    u = (rng.uniform(size=(n_part, T)) > 0.5).astype(np.float32)
+    y = (rng.uniform(size=(n_part, T)) > 0.5).astype(np.float32)
+    params = np.stack([rng.uniform(-6, -3, n), rng.uniform(-6, -3, n), np.exp(rng.uniform(-0.3, 0.8, n))]).astype(np.float32)
+    group = (np.arange(n) % 7).astype(np.int32)
+    net = nets.binary3(G.Network)
+    net.create_belief_propagation_fn()
+    plan = net.plan
+    attr = net._flatten(plan)
+    slots = (C.c_int32 * 3)(plan.slot(1, "tonic_volatility"), plan.slot(2, "tonic_volatility"), plan.slot(-1, "response_parameter", 0))
+    out = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("HGF_HOST_CHUNKS", flag)
+        logp, grad, red = np.zeros(n, np.float32), np.zeros((3, n), np.float32), np.zeros(7, np.float32)
+        call = _lib.Call()
+        call.dtype, call.n_instances, call.n_steps = 32, n, T
+        call.input_group_size = call.response_group_size = 0 if shared else n_chain
+        call.input_data, call.response_inputs, call.attributes = u.ctypes.data, y.ctypes.data, attr.ctypes.data
+        call.n_params, call.param_slots, call.params = 3, C.cast(slots, C.POINTER(C.c_int32)), params.ctypes.data
+        call.response_fn = _lib.RESPONSES["binary_softmax_inverse_temperature"]
+        call.surprise_sum, call.gradient, call.reduced, call.group = logp.ctypes.data, grad.ctypes.data, red.ctypes.data, group.ctypes.data
+        call.out_scale = -1.0
+        before = _lib.launch_count()
+        _lib.check(_lib.lib().hgf_logp_grad_host(plan.handle, C.byref(call), 0))
+        out[flag] = (logp, grad, red, _lib.launch_count() - before)
+    assert out["1"][3] == 4 and out["0"][3] == 1                     # four slices vs one launch
+    assert np.array_equal(out["1"][0], out["0"][0]) and np.array_equal(out["1"][1], out["0"][1])
+    assert np.isfinite(out["1"][0]).all()
+    assert np.allclose(out["1"][2], out["0"][2], rtol=1e-5)          # atomics: order differs
