@@ -774,3 +774,48 @@ def test_host_entry_point_chunk_pipeline(G, n_part, n_chain, shared, monkeypatch
     assert np.array_equal(out["1"][0], out["0"][0]) and np.array_equal(out["1"][1], out["0"][1])
     assert np.isfinite(out["1"][0]).all()
     assert np.allclose(out["1"][2], out["0"][2], rtol=1e-5)          # atomics: order differs
+
+
+def test_committed_golden_vectors(G, R, datasets):
+    """The CUDA path against tests/golden/oracle_vectors.npz (float64 oracle results, committed): float64 launches to
+    1e-9, float32 launches to the stated tolerances on the instances that are well-conditioned (float32 and float64
+    oracle agree to 1e-5); no oracle code runs in this test."""
+    import os
+
+    v = np.load(os.path.join(os.path.dirname(__file__), "golden", "oracle_vectors.npz"))
+    for name, build, data in (("binary3", nets.binary3, datasets["u"]), ("continuous3", nets.continuous3, datasets["x"]),
+                              ("ghgf16", nets.ghgf16, nets.ar1_series(200))):
+        for dtype, rtol, atol in (("float64", 1e-9, 1e-12), ("float32", RTOL_TRAJ, 1e-6)):
+            g = build(G.Network, dtype=dtype).input_data(data)
+            for node in range(len(g.edges)):
+                for k in nets.BELIEFS:
+                    got = np.asarray(g.node_trajectories[node][k], dtype=np.float64)
+                    assert np.allclose(got, v[f"traj/{name}/{node}/{k}"], rtol=rtol, atol=atol, equal_nan=True), (name, dtype, node, k)
+    keys = [(1, "tonic_volatility"), (2, "tonic_volatility"), ("response_parameter", 0)]
+    p = v["config4/params"]
+    for dtype in ("float64", "float32"):
+        res = nets.binary3(G.Network, dtype=dtype).batch(datasets["u"], dict(zip(keys, p)), response_function=R.binary_softmax_inverse_temperature,
+                                                         response_function_inputs=datasets["y"], gradient=True)
+        s = res.surprise.double().cpu().numpy()
+        if dtype == "float64":
+            assert np.allclose(s, v["config4/surprise"], rtol=1e-9)
+            for i, k in enumerate(keys):
+                assert np.allclose(res.gradient[k].cpu().numpy(), v["config4/gradient"][i], rtol=1e-7, atol=1e-9)
+        else:
+            well = np.abs(v["config4/surprise_f32"] / v["config4/surprise"] - 1) <= 1e-5
+            assert well.mean() > 0.8 and np.allclose(s[well], v["config4/surprise"][well], rtol=RTOL_SUM)
+            for i, k in enumerate(keys):
+                gg, want = res.gradient[k].double().cpu().numpy(), v["config4/gradient"][i]
+                assert np.allclose(gg[well], want[well], rtol=1e-3, atol=1e-3 * np.abs(want).max()), k
+    keys = [(i, "tonic_volatility") for i in (1, 2, 3)]
+    for dtype in ("float64", "float32"):
+        res = nets.continuous3(G.Network, dtype=dtype).batch(datasets["x"], dict(zip(keys, v["config2/params"])),
+                                                             response_function=R.first_level_gaussian_surprise)
+        s, want = res.surprise.double().cpu().numpy(), v["config2/surprise"]
+        fin = np.isfinite(want)
+        assert np.array_equal(fin, np.isfinite(s))
+        if dtype == "float64":
+            assert np.allclose(s[fin], want[fin], rtol=1e-8, atol=1e-7)
+        else:
+            well = fin & (np.abs(v["config2/surprise_f32"] - want) <= 1e-5 * (np.abs(want) + 1))
+            assert np.allclose(s[well], want[well], rtol=RTOL_SUM, atol=1e-2)

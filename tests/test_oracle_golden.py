@@ -433,3 +433,22 @@ def test_to_pandas_notebook_goldens(datasets):
     assert close(df.x_1_surprise.sum(), -2446.2734)
     assert close(df.x_2_surprise.sum(), 665.03186)
     assert list(df.columns[:2]) == ["time_steps", "time"] and "x_1_expected_precision" in df.columns
+
+
+# --------------------------------------------------------------------------- committed fixtures (tests/golden/)
+def test_oracle_reproduces_the_committed_vectors():
+    """tests/golden/oracle_vectors.npz (written by tests/golden/make_oracle_vectors.py) is what the oracle gives today."""
+    import os
+
+    import nets
+
+    v = np.load(os.path.join(os.path.dirname(__file__), "golden", "oracle_vectors.npz"))
+    d = np.load(os.path.join(os.path.dirname(__file__), "..", "pyhgf_b200", "data", "datasets.npz"))
+    net = nets.binary3(Network, dtype="float64").input_data(d["binary_u"])
+    for node in (1, 2):
+        for k in nets.BELIEFS:
+            assert np.allclose(net.node_trajectories[node][k], v[f"traj/binary3/{node}/{k}"], rtol=1e-12, atol=0, equal_nan=True)
+    o = nets.binary3(Network, dtype="float64").create_belief_propagation_fn()
+    slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
+    s, g = o.batch_grad(d["binary_u"], slots, v["config4/params"], "binary_softmax_inverse_temperature", resp_inputs=d["binary_y"])
+    assert np.allclose(s, v["config4/surprise"], rtol=1e-12) and np.allclose(g, v["config4/gradient"], rtol=1e-9)
