@@ -470,7 +470,7 @@ def test_config5_trajectories_layout(G, datasets):
                 assert np.allclose(got, single.node_trajectories[i][k], rtol=RTOL_TRAJ, atol=1e-6), (n_i, i, k)
 
 
-@pytest.mark.parametrize("net_name,n", [("ghgf16", 260), ("ghgf16", 1000), ("binary3", 64), ("multi_child", 333)])
+@pytest.mark.parametrize("net_name,n", [("ghgf16", 260), ("ghgf16", 1000), ("binary3", 64), ("multi_child", 333), ("ghgf16_all", 200)])
 @pytest.mark.parametrize("dtype", ["float32", "float64"])
 def test_tma_trajectory_writeback_is_bit_identical(G, datasets, net_name, n, dtype, monkeypatch):
     """Trajectories written through shared-memory staging + one TMA tensor store per block-step equal, bit for
@@ -488,6 +488,8 @@ def test_tma_trajectory_writeback_is_bit_identical(G, datasets, net_name, n, dty
         data, build, nodes = nets.ar1_series(150), nets.ghgf16, tuple(range(4, 12))
     params = {(i, "tonic_volatility"): rng.normal(-4, 0.5, n) for i in nodes}
     record = [(i, k) for i in nodes for k in nets.BELIEFS]
+    if net_name == "ghgf16_all":  # all 80 leaves: 80 KB of staging tiles in float64 (> 48 KB: opt-in dynamic shared memory)
+        record = [(i, k) for i in range(16) for k in nets.BELIEFS + (("mean_vol", "expected_mean_vol", "precision_vol", "expected_precision_vol") if i >= 12 else ())]
     out = {}
     for flag in ("0", "1"):
         monkeypatch.setenv("HGF_NO_TMA", flag)
