@@ -821,3 +821,33 @@ def test_committed_golden_vectors(G, R, datasets):
         else:
             well = fin & (np.abs(v["config2/surprise_f32"] - want) <= 1e-5 * (np.abs(want) + 1))
             assert np.allclose(s[well], want[well], rtol=RTOL_SUM, atol=1e-2)
+
+
+def test_plain_c_caller_of_the_abi(G, datasets, tmp_path):
+    """examples/c_abi_binary3.c: a C program (gcc, no Python / torch in the process) builds the 3-level binary HGF's
+    topology by hand, calls hgf_plan_create / hgf_filter_host and gets the oracle's surprise."""
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.join(root, "pyhgf_b200", "lib")
+    exe = str(tmp_path / "c_abi_binary3")
+    subprocess.run(["gcc", "-O2", "-I", os.path.join(root, "include"), os.path.join(root, "examples", "c_abi_binary3.c"), "-L", lib_dir,
+                    "-lpyhgf_cuda", f"-Wl,-rpath,{lib_dir}", "-o", exe], check=True)
+    np.savetxt(tmp_path / "u.txt", datasets["u"], fmt="%d")
+    n = 257
+    r = subprocess.run([exe, str(tmp_path / "u.txt"), str(n), str(tmp_path / "out.txt")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "kernel: static:binary3" in r.stdout and "launches: 1" in r.stdout
+    out = np.loadtxt(tmp_path / "out.txt")
+    assert out.shape == (n, 3)
+    o = nets.binary3(onet.Network).create_belief_propagation_fn()
+    want = o.batch_surprise(datasets["u"], [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility")], out[:, :2].T.copy(),
+                            "first_level_binary_surprise")
+    o64 = nets.binary3(onet.Network, dtype="float64").create_belief_propagation_fn()
+    want64 = o64.batch_surprise(datasets["u"], [o64.slot(1, "tonic_volatility"), o64.slot(2, "tonic_volatility")], out[:, :2].T.copy(),
+                                "first_level_binary_surprise")
+    well = np.abs(want / want64 - 1) <= 1e-5
+    assert well.mean() > 0.7 and np.allclose(out[well, 2], want[well], rtol=RTOL_SUM)
+    # the defaults written out by hand in the C file are the front-end's: omega = -4 reproduces the reference golden
+    assert np.isfinite(out[:, 2]).all()
