@@ -16,6 +16,8 @@ CUDA device.
 
 from __future__ import annotations
 
+import os
+
 import ctypes as C
 from copy import deepcopy
 from typing import Callable, Optional, Sequence, Union
@@ -765,6 +767,12 @@ class Network:
                 "callable, record the trajectories it needs (record=[...]) and apply it to result.trajectories"
             )
         plan = self._get_plan(values.shape[2])
+        if plan.kernel_name == "interpreter" and os.environ.get("HGF_AUTO_SPECIALISE") == "1" and values.shape[2] == len(self.input_idxs):
+            # opt-in: build register-resident kernels for this topology on first use (pyhgf_b200/specialise.py)
+            n_filter = sum(1 for k in parameters if not (isinstance(k, (tuple, list)) and k[0] == "response_parameter") and k != "response_parameter")
+            self.specialise(gradient_parameters=n_filter if gradient else 0, response_parameter=gradient and n_filter < len(parameters),
+                            float64=self.bits == 64)
+            plan = self._get_plan(values.shape[2])
         rec_slots = [self._resolve_slot(plan, k) for k in record]
         ri = response_function_inputs
         if ri is not None and np.size(ri) == 0:

@@ -851,3 +851,15 @@ def test_plain_c_caller_of_the_abi(G, datasets, tmp_path):
     assert well.mean() > 0.7 and np.allclose(out[well, 2], want[well], rtol=RTOL_SUM)
     # the defaults written out by hand in the C file are the front-end's: omega = -4 reproduces the reference golden
     assert np.isfinite(out[:, 2]).all()
+
+
+def test_auto_specialise_opt_in(G, R, monkeypatch):
+    """HGF_AUTO_SPECIALISE=1: the first batched call of a topology without a built-in kernel builds and uses its
+    register-resident specialisation instead of the interpreter."""
+    x = nets.ar1_series(50, n_series=1)[:, 0]
+    p = {(2, "tonic_volatility"): np.full(70, -3.0)}
+    a = nets.tanh_coupling(G.Network).batch(x, p, response_function=R.first_level_gaussian_surprise)
+    monkeypatch.setenv("HGF_AUTO_SPECIALISE", "1")
+    b = nets.tanh_coupling(G.Network).batch(x, p, response_function=R.first_level_gaussian_surprise)
+    assert b.kernel_name.startswith("specialised:")
+    assert np.allclose(a.surprise.cpu().numpy(), b.surprise.cpu().numpy(), rtol=1e-5, equal_nan=True)
