@@ -364,9 +364,12 @@ template <class B> __device__ __forceinline__ void fused_all_reduce(const ScanAr
 // Occupancy: BASELINE config 4 gives each GPU 65 536 instances = 13.8 warps per SM; the float32 register-
 // resident kernels are bounded to 7 resident 64-thread blocks (<= 144 registers) so that the whole batch
 // is co-resident in one wave instead of 1.7 (a second, mostly empty wave costs ~40 %).
+#ifndef HGF_WIDE_MIN_BLOCKS
+#define HGF_WIDE_MIN_BLOCKS 1  // resident 64-thread blocks per SM asked of the wide (> 4 nodes) float32 specialisations
+#endif
 template <class T, class Topo> constexpr int scan_min_blocks() {
   if constexpr (!Topo::is_static) return 1; else
-  return (Topo::is_static && sizeof(base_t<T>) == 4 && Topo::kNodes <= 4) ? 7 : 1;
+  return (sizeof(base_t<T>) == 4 && Topo::kNodes <= 4) ? 7 : (sizeof(base_t<T>) == 4 ? HGF_WIDE_MIN_BLOCKS : 1);
 }
 
 template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT, bool REC>
