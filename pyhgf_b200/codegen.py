@@ -86,6 +86,21 @@ def _ghgf16():
     return g
 
 
+def _ghgf8():
+    """One connected component of the 16-node gHGF above (its two components are isomorphic): what
+    ``Network.batch`` launches per component when it splits a disconnected network (network.py)."""
+    g = _Graph()
+    g.add(2)
+    g.add(2)
+    g.add(2, value_children=[0])
+    g.add(2, value_children=[1])
+    g.add(2, volatility_children=[2])
+    g.add(2, volatility_children=[3])
+    g.add(6, value_children=[2, 3])
+    g.add(6, value_children=[6])
+    return g
+
+
 #: name -> (graph factory, volatility_updates, mean_field, float32 kernels, float64 kernels); a kernel is
 #: (PF, PR): PF filter tangent directions, PR response-parameter-only tangent directions (0 or 1)
 _ALL = tuple((pf, pr) for pr in (0, 1) for pf in range(5))
@@ -95,6 +110,7 @@ TOPOLOGIES = {
     "continuous2": (lambda: _continuous(2), "unbounded", False, ((0, 0), (3, 0)), ((0, 0),)),
     "continuous3": (lambda: _continuous(3), "unbounded", False, ((0, 0), (3, 0), (4, 0)), ((0, 0),)),
     "ghgf16": (_ghgf16, "unbounded", False, ((0, 0),), ()),
+    "ghgf8": (_ghgf8, "unbounded", False, ((0, 0),), ()),
 }
 
 

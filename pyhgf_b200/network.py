@@ -143,6 +143,26 @@ class BatchResult:
         return {k: -v for k, v in self.gradient.items()}
 
 
+class ComponentsResult(BatchResult):
+    """Outputs of a batched launch that ``Network.batch`` split over the network's connected components
+    (one launch per component, on its own stream): the same fields as :class:`BatchResult`, keys in the
+    original node numbering."""
+
+    def __init__(self, parts, streams, device):
+        super().__init__()
+        self._parts, self._streams, self._device = parts, streams, device
+        self.kernel_name = f"components({len(parts)}): " + " | ".join(p.kernel_name for p in parts)
+
+    def relaunch(self, stream=None):
+        cur = torch.cuda.current_stream(self._device) if stream is None else stream
+        for part, s in zip(self._parts, self._streams):
+            s.wait_stream(cur)
+            part.relaunch(stream=s)
+        for s in self._streams:
+            cur.wait_stream(s)
+        return self
+
+
 class Network:
     """A predictive-coding network whose belief propagation runs on a B200.
 
@@ -285,6 +305,43 @@ class Network:
 
     def _invalidate_plan(self):
         self._plan = None
+
+    def connected_components(self) -> list:
+        """The node sets of the network's connected components (any coupling kind), each sorted, ordered by first node."""
+        parent = list(range(self.n_nodes))
+
+        def find(i):
+            while parent[i] != i:
+                parent[i] = parent[parent[i]]
+                i = parent[i]
+            return i
+
+        for i, e in enumerate(self.edges):
+            for kind in ("value_parents", "volatility_parents", "value_children", "volatility_children"):
+                for j in getattr(e, kind) or ():
+                    parent[find(i)] = find(j)
+        groups: dict = {}
+        for i in range(self.n_nodes):
+            groups.setdefault(find(i), []).append(i)
+        return sorted(groups.values(), key=lambda g: g[0])
+
+    def _component_network(self, nodes):
+        """The sub-network of one connected component, nodes renumbered in ascending order; attributes are copied
+        from this network at call time (they may have been edited since the last call)."""
+        local = {g: k for k, g in enumerate(nodes)}
+        sub = Network(volatility_updates=self.volatility_updates, max_posterior_precision=self.max_posterior_precision,
+                      mean_field_updates=self.mean_field_updates, precision_clipping_value=self.attributes[-1]["precision_clipping_value"],
+                      dtype="float32" if self.bits == 32 else "float64", device=self._device)
+        remap = lambda t: None if t is None else tuple(local[j] for j in t)  # noqa: E731
+        sub.edges = tuple(AdjacencyLists(self.edges[g].node_type, remap(self.edges[g].value_parents), remap(self.edges[g].volatility_parents),
+                                         remap(self.edges[g].value_children), remap(self.edges[g].volatility_children),
+                                         self.edges[g].coupling_fn) for g in nodes)
+        sub.n_nodes = len(nodes)
+        for g in nodes:
+            sub.attributes[local[g]] = deepcopy(self.attributes[g])
+        sub.attributes[-1] = deepcopy(self.attributes[-1])
+        sub._input_idxs = tuple(local[g] for g in self.input_idxs if g in local)
+        return sub, local
 
     def specialise(self, gradient_parameters: int = 0, response_parameter: bool = False, float64: bool = False,
                    verbose: bool = False) -> str:
@@ -723,6 +780,82 @@ class Network:
         return res.pointwise[0].cpu().numpy()
 
     # ------------------------------------------------------------------ batch
+    def _split_over_components(self, input_data, parameters, response_function, response_function_inputs,
+                               response_function_parameters, time_steps, observed, n_instances, input_group_size,
+                               response_group_size, record, last_attributes, pointwise, gradient, n_groups, out_scale, stream,
+                               fused_reduce):
+        """A network made of several disconnected sub-networks IS several independent networks: run one launch per
+        connected component, concurrently on separate streams.  Per instance that is more threads with fewer nodes
+        each -- a shorter serial chain per time step and half the registers for BASELINE config 5's 16-node network
+        (two 8-node components).  Only the plain evaluations are split (no gradient, final attributes or device
+        reduction, no response function -- those read across components); everything else, and
+        HGF_SPLIT_COMPONENTS=0, takes the single-launch path.  Returns None when the call is not split."""
+        if os.environ.get("HGF_SPLIT_COMPONENTS") == "0" or gradient or last_attributes or n_groups or fused_reduce is not None:
+            return None
+        comps = self.connected_components()
+        if len(comps) < 2:
+            return None
+        if response_function is not None or pointwise or not record:
+            return None  # response functions read across components (input nodes, node 1): single launch
+        grouped = input_group_size > 0
+        x = torch.as_tensor(np.asarray(input_data) if not torch.is_tensor(input_data) else input_data)
+        want_dim = 3 if grouped else 2
+        if x.ndim == want_dim - 1:
+            x = x.unsqueeze(-1)
+        inputs = list(self.input_idxs)
+        if x.ndim != want_dim or x.shape[-1] != len(inputs):
+            return None
+        obs = None
+        if observed is not None:
+            if isinstance(observed, (tuple, list)) and not grouped:
+                observed = np.stack([np.asarray(o) for o in observed], axis=1)
+            obs = torch.as_tensor(np.asarray(observed) if not torch.is_tensor(observed) else observed)
+            if obs.ndim == want_dim - 1:
+                obs = obs.unsqueeze(-1)
+            if obs.shape != x.shape:
+                return None
+        if n_instances is None:
+            sizes = {int(np.size(v)) if not torch.is_tensor(v) else int(v.numel()) for v in parameters.values()} - {1}
+            if len(sizes) > 1:
+                raise ValueError(f"per-instance parameters disagree on the batch size: {sorted(sizes)}")
+            n_instances = sizes.pop() if sizes else (x.shape[0] * input_group_size if grouped else 1)
+        dev = self.device
+        cur = torch.cuda.current_stream(dev) if stream is None else stream
+        parts, streams, merged_traj = [], [], {}
+        for nodes in comps:
+            sub, local = self._component_network(nodes)
+            cols = [c for c, g in enumerate(inputs) if g in local]
+            rec_k = [(local[int(n)], f) for n, f in record if int(n) in local]
+            if not rec_k:
+                continue  # nothing is asked of this component
+            p_k = {}
+            for key, val in parameters.items():
+                if isinstance(key, str) or key[0] == "response_parameter":
+                    continue  # no response function on this path
+                if key[0] == "precision_clipping_value" or key[0] == -1:
+                    p_k[key] = val
+                elif int(key[0]) in local:
+                    p_k[(local[int(key[0])],) + tuple(key[1:])] = val
+            s_k = torch.cuda.Stream(device=dev)
+            s_k.wait_stream(cur)
+            with torch.cuda.stream(s_k):
+                r = sub.batch(x[..., cols], p_k, time_steps=time_steps, observed=None if obs is None else obs[..., cols],
+                              n_instances=n_instances, input_group_size=input_group_size, record=rec_k, stream=s_k)
+            if getattr(r, "_traj", None) is not None:
+                r._traj.record_stream(cur)  # allocated on the side stream, read on the caller's
+            back = {v: g for g, v in local.items()}
+            for (n_loc, f), t in r.trajectories.items():
+                merged_traj[(back[n_loc], f)] = t
+            parts.append(r)
+            streams.append(s_k)
+        if not parts:
+            return None
+        for s_k in streams:
+            cur.wait_stream(s_k)
+        out = ComponentsResult(parts, streams, dev)
+        out.trajectories = {tuple(key): merged_traj[(int(key[0]), key[1])] for key in record}
+        return out
+
     def batch(self, input_data, parameters: Optional[dict] = None, *, response_function=None,
               response_function_inputs=None, response_function_parameters=None, time_steps=None, observed=None,
               n_instances: Optional[int] = None, input_group_size: int = 0, response_group_size: int = 0,
@@ -750,6 +883,12 @@ class Network:
         if self.scan_fn is None:
             self.create_belief_propagation_fn()
         dev = self.device
+        split = self._split_over_components(input_data, parameters, response_function, response_function_inputs,
+                                            response_function_parameters, time_steps, observed, n_instances, input_group_size,
+                                            response_group_size, record, last_attributes, pointwise, gradient, n_groups, out_scale,
+                                            stream, fused_reduce)
+        if split is not None:
+            return split
         grouped = input_group_size > 0
         values, obs = self._format_series(input_data, observed, dev, grouped=grouped)
         if n_instances is None:

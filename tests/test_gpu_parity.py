@@ -863,3 +863,33 @@ def test_auto_specialise_opt_in(G, R, monkeypatch):
     b = nets.tanh_coupling(G.Network).batch(x, p, response_function=R.first_level_gaussian_surprise)
     assert b.kernel_name.startswith("specialised:")
     assert np.allclose(a.surprise.cpu().numpy(), b.surprise.cpu().numpy(), rtol=1e-5, equal_nan=True)
+
+
+def test_disconnected_network_is_split_over_components(G, monkeypatch):
+    """BASELINE config 5's 16-node network has two connected components: `Network.batch` runs them as two concurrent
+    8-node launches (register-resident `static:ghgf8`) and returns the trajectories of the single 16-node launch."""
+    import torch
+
+    net = nets.ghgf16(G.Network)
+    assert net.connected_components() == [[0, 1, 4, 5, 8, 9, 12, 14], [2, 3, 6, 7, 10, 11, 13, 15]]
+    x = nets.ar1_series(300)
+    n = 700
+    rng = np.random.default_rng(4)
+    params = {(i, "tonic_volatility"): rng.normal(-4, 0.5, n) for i in range(4, 12)}
+    params.update({(i, "tonic_volatility_vol"): rng.normal(-4, 0.5, n) for i in range(12, 16)})
+    record = [(i, k) for i in range(16) for k in nets.BELIEFS + (("mean_vol", "precision_vol") if i >= 12 else ())]
+    obs = (rng.uniform(size=x.shape) > 0.05).astype(np.uint8)
+    out = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("HGF_SPLIT_COMPONENTS", flag)
+        res = nets.ghgf16(G.Network).batch(x, params, record=record, observed=obs, time_steps=np.full(300, 0.5))
+        res.relaunch()
+        torch.cuda.synchronize()
+        out[flag] = res
+    assert out["1"].kernel_name == "components(2): static:ghgf8 | static:ghgf8" and out["0"].kernel_name == "static:ghgf16"
+    for k in record:
+        a, b = out["1"].trajectories[k], out["0"].trajectories[k]
+        assert a.shape == b.shape == (n, 300)
+        assert torch.allclose(a, b, rtol=1e-6, atol=1e-7, equal_nan=True), k
+    # a connected network, a call with a response function or a gradient are not split
+    assert nets.binary3(G.Network).connected_components() == [[0, 1, 2]]
