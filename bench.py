@@ -236,7 +236,13 @@ def run_gpu(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = os.environ.get("HGF_NCCL_DEBUG", "WARN")  # keep NCCL's banner off stdout: one JSON line only
+        # stdout carries ONE JSON line: NCCL prints its version banner there at any NCCL_DEBUG level >= VERSION, so its
+        # log goes to stderr (and is off unless HGF_NCCL_DEBUG asks for a level)
+        os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
+        if os.environ.get("HGF_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = os.environ["HGF_NCCL_DEBUG"]
+        else:
+            os.environ.pop("NCCL_DEBUG", None)
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()
 

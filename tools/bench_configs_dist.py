@@ -19,7 +19,7 @@ rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_S
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 if world > 1:
-    os.environ["NCCL_DEBUG"] = "WARN"
+    os.environ.pop("NCCL_DEBUG", None)  # the image sets NCCL_DEBUG=VERSION: keep the banner off stdout
     dist.init_process_group("nccl", device_id=dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
