@@ -168,6 +168,28 @@ int hgf_logp_grad_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t d
 int64_t hgf_fused_reduce_bytes(int32_t n_groups, int32_t dtype);
 int64_t hgf_fused_reduce_result_offset(int32_t n_groups, int32_t dtype, uint32_t epoch);
 
+/* Exponential-family state node with a fixed learning rate ("generalised Bayesian filtering":
+ * add_nodes(kind="ef-state", learning="generalised-filtering"), pyhgf/model/add_nodes.py:360-470;
+ * prediction_error_update_exponential_family_fixed, pyhgf/updates/prediction_error/exponential.py:13-60).
+ * The node has no parents: at every step   xis <- xis + (t(x) - xis) / (1 + nu)   where observed, with the
+ * sufficient statistics t(x) = [x, vech_rowwise_lower(x x^T)] of a (multivariate) normal (pyhgf/math.py:90-92,
+ * MultivariateNormal.sufficient_statistics_from_observations), K = d + d (d + 1) / 2 values.  N instances differ
+ * in their learning rate nu (a sweep) and/or their series. */
+typedef struct {
+  int32_t dtype;               /* 32 or 64 */
+  int64_t n_instances;         /* N */
+  int32_t n_steps;             /* T */
+  int32_t dimension;           /* d <= 8 */
+  int64_t input_group_size;    /* instance n reads series n / input_group_size (0: one shared series) */
+  const void* input_data;      /* [G][T][d] */
+  const uint8_t* observed;     /* [G][T] or NULL */
+  const void* nus;             /* [N] */
+  const void* xis0;            /* [K] initial sufficient statistics, shared */
+  void* xis_trajectory;        /* [K][T][N] or NULL */
+  void* xis_last;              /* [K][N] or NULL */
+} hgf_ef_call_t;
+int hgf_ef_filter(const hgf_ef_call_t* call, void* stream);       /* device pointers */
+
 /* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
 int64_t hgf_launch_count(void);
 

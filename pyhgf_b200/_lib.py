@@ -111,10 +111,28 @@ EXPORTS = (
     "hgf_abi_version", "hgf_last_error", "hgf_plan_create", "hgf_plan_destroy", "hgf_plan_n_slots",
     "hgf_plan_slot_coupling", "hgf_plan_slot_clipping", "hgf_plan_slot_response", "hgf_plan_kernel_name",
     "hgf_filter", "hgf_logp_grad", "hgf_filter_host", "hgf_logp_grad_host", "hgf_launch_count",
-    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_register_specialisation",
+    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_register_specialisation", "hgf_ef_filter",
 )
 
 _lib = None
+
+
+class EfCall(C.Structure):
+    """``hgf_ef_call_t``"""
+
+    _fields_ = [
+        ("dtype", C.c_int32),
+        ("n_instances", C.c_int64),
+        ("n_steps", C.c_int32),
+        ("dimension", C.c_int32),
+        ("input_group_size", C.c_int64),
+        ("input_data", C.c_void_p),
+        ("observed", C.c_void_p),
+        ("nus", C.c_void_p),
+        ("xis0", C.c_void_p),
+        ("xis_trajectory", C.c_void_p),
+        ("xis_last", C.c_void_p),
+    ]
 
 
 class BackendError(RuntimeError):
@@ -156,6 +174,8 @@ def lib() -> C.CDLL:
         f.argtypes = [C.c_void_p, C.POINTER(Call), C.c_int32]
         f.restype = C.c_int
     L.hgf_launch_count.restype = C.c_int64
+    L.hgf_ef_filter.argtypes = [C.POINTER(EfCall), C.c_void_p]
+    L.hgf_ef_filter.restype = C.c_int
     L.hgf_register_specialisation.argtypes = [C.c_char_p]
     L.hgf_register_specialisation.restype = C.c_int
     L.hgf_fused_reduce_bytes.argtypes = [C.c_int32, C.c_int32]

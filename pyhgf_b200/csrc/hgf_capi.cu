@@ -35,6 +35,11 @@ static int fail(const char* fmt, ...) {
   return 1;
 }
 
+namespace hgf {  // shared with the other entry-point translation units (hgf_ef.cu)
+void count_launches(int n) { g_launches += n; }
+int report_error(const char* msg) { return fail("%s", msg); }
+}  // namespace hgf
+
 struct hgf_plan {
   Program prog;
   const KernelVariant* variant;

@@ -25,7 +25,7 @@ from typing import Callable, Optional, Sequence, Union
 import numpy as np
 import torch
 
-from . import _lib
+from . import _lib, ef_state
 from .topology import AdjacencyLists, Plan, get_update_sequence
 
 _COUPLING_KEYS = ("value_coupling_parents", "volatility_coupling_parents", "value_coupling_children",
@@ -69,7 +69,7 @@ def _binary_state_defaults() -> dict:  # add_nodes.py:330-340
 
 _NODE_KINDS = {"continuous-state": (2, _continuous_state_defaults), "volatile-state": (6, _volatile_state_defaults),
                "binary-state": (1, _binary_state_defaults)}
-_OTHER_KINDS = ("dp-state", "ef-state", "categorical-state", "constant-state")
+_OTHER_KINDS = ("dp-state", "categorical-state", "constant-state")
 
 
 def get_couplings(value_parents, volatility_parents, value_children, volatility_children):
@@ -201,7 +201,7 @@ class Network:
                   value_children=None, value_parents=None, volatility_children=None, volatility_parents=None,
                   coupling_fn: tuple = (None,), **additional_parameters):
         """Add state node(s) (network.py:778-945; defaults add_nodes.py:65-85, 159-184, 330-340)."""
-        if kind not in _NODE_KINDS and kind not in _OTHER_KINDS:
+        if kind not in _NODE_KINDS and kind not in _OTHER_KINDS and kind != "ef-state":
             raise ValueError(
                 "Invalid node type. Should be one of the following: 'dp-state', 'continuous-state', 'binary-state', "
                 "'ef-state', 'categorical-state', 'volatile-state', or 'constant-state'"
@@ -209,8 +209,10 @@ class Network:
         if kind in _OTHER_KINDS:
             raise NotImplementedError(
                 f"'{kind}' nodes are outside the belief-propagation path this backend accelerates "
-                "(binary-, continuous- and volatile-state nodes)"
+                "(binary-, continuous- and volatile-state nodes, ef-state nodes with a fixed learning rate)"
             )
+        if kind == "ef-state":
+            return self._add_ef_state(n_nodes, node_parameters, additional_parameters, value_children)
         vp, volp, vc, volc = get_couplings(value_parents, volatility_parents, value_children, volatility_children)
         node_type, make_defaults = _NODE_KINDS[kind]
         if node_type == 6:  # the volatility level is implicit (add_nodes.py:106-202)
@@ -253,6 +255,36 @@ class Network:
             self.n_nodes += 1
         self._invalidate()
         return self
+
+    def _add_ef_state(self, n_nodes, node_parameters, additional_parameters, value_children):
+        """Exponential-family state node(s), add_nodes.py:360-470 (fixed learning rate only, see ef_state.py)."""
+        if value_children is not None:
+            raise NotImplementedError("an ef-state node with value children is outside the accelerated path")
+        params = ef_state.defaults()
+        unknown = [k for k in additional_parameters if k not in params]
+        if unknown:
+            raise ValueError(
+                f"Some parameter(s) passed as keyword arguments were not found in the default key(s) of a ef-state node "
+                f"(i.e. {list(params.keys())}). If you want to create a new key in the node's attributes, "
+                "please use the node_parameters argument instead."
+            )
+        params.update(additional_parameters)
+        params.update(node_parameters or {})
+        params = ef_state.finish_parameters(params)
+        for _ in range(n_nodes):
+            self.edges = self.edges + (AdjacencyLists(ef_state.NODE_TYPE, None, None, None, None, (None,)),)
+            self.attributes[self.n_nodes] = deepcopy(params)
+            self.n_nodes += 1
+        self._invalidate()
+        return self
+
+    def _ef_nodes(self) -> list:
+        """The ef-state nodes, after checking that the network is one this backend runs: the hgf_ef_filter path
+        serves networks made of ef-state nodes only (they have no parents, so nothing couples them to HGF nodes)."""
+        ef = [i for i, e in enumerate(self.edges) if e.node_type == ef_state.NODE_TYPE]
+        if ef and len(ef) != len(self.edges):
+            raise NotImplementedError("ef-state nodes and HGF nodes in one network: filter them as two networks")
+        return ef
 
     def add_edges(self, parent_idxs, children_idxs, kind: str = "value", coupling_strengths=1.0,
                   coupling_fn: tuple = (None,)):
@@ -384,6 +416,11 @@ class Network:
     def create_belief_propagation_fn(self, overwrite: bool = True):
         """Derive the static schedule and lower the network into a CUDA plan (network.py:182-234)."""
         _ = self.input_idxs
+        if self._ef_nodes():  # get_input_dimension, network.py:1069-1086; the schedule is one PE step per node
+            self.input_dim = [int(self.attributes[i]["dimension"]) for i in self.input_idxs]
+            self.update_sequence = ((), tuple((i, "prediction_error_update_exponential_family_fixed") for i in self.input_idxs))
+            self.scan_fn = True
+            return self
         self.input_dim = [1 for _ in self.input_idxs]
         if self.update_sequence is None or overwrite:
             self.update_sequence = get_update_sequence(self, self.volatility_updates, self.mean_field_updates)
@@ -636,6 +673,8 @@ class Network:
             self.input_idxs = input_idxs
         if self.scan_fn is None:
             self.create_belief_propagation_fn()
+        if self._ef_nodes():
+            return self._ef_input_data(input_data, time_steps, observed, record_trajectories)
         dev = self.device
         values, obs = self._format_series(input_data, observed, dev, grouped=False)
         plan = self._get_plan(values.shape[2])
@@ -674,6 +713,109 @@ class Network:
             self.node_trajectories = None
         self._last_inputs = (input_data, time_steps, observed)
         return self
+
+    # ---------------------------------------------------- ef-state networks
+    def _ef_columns(self, n_columns: int) -> list:
+        """[(node, first column, dimension)]: the split of network.py:603-604 over the input nodes."""
+        out, col = [], 0
+        for i in self.input_idxs:
+            d = int(self.attributes[i]["dimension"])
+            out.append((i, col, d))
+            col += d
+        if n_columns != col:
+            raise ValueError(f"input_data has {n_columns} column(s) but the input nodes take {col}")
+        return out
+
+    def _ef_input_data(self, input_data, time_steps, observed, record_trajectories):
+        dev = self.device
+        dt, cast = _torch_dtype(self.bits), _np_dtype(self.bits)
+        x = np.asarray(input_data.cpu() if torch.is_tensor(input_data) else input_data, dtype=cast)
+        if x.ndim == 1:
+            x = x[:, None]
+        T = x.shape[0]
+        cols = self._ef_columns(x.shape[1])
+        if observed is None:
+            masks = [None] * len(cols)
+        elif isinstance(observed, (tuple, list)):
+            masks = [np.asarray(o) for o in observed]
+        else:
+            o = np.asarray(observed)
+            masks = [o] if o.ndim == 1 else [o[:, k] for k in range(o.shape[1])]
+        ts = np.ones(T) if time_steps is None else np.asarray(time_steps, dtype=np.float64)
+        last, nt = deepcopy(self.attributes), {}
+        for (i, c0, d), m in zip(cols, masks):
+            a = self.attributes[i]
+            series = torch.as_tensor(np.ascontiguousarray(x[None, :, c0:c0 + d])).to(dev)
+            obs = None if m is None else torch.as_tensor((m != 0).astype(np.uint8)[None]).to(dev).contiguous()
+            nus = torch.full((1,), float(a["nus"]), dtype=dt, device=dev)
+            traj, fin = ef_state.launch(bits=self.bits, device=dev, series=series, observed=obs, nus=nus, xis0=a["xis"],
+                                        dimension=d, input_group_size=0, want_trajectory=record_trajectories)
+            seen = np.ones(T, dtype=np.int64) if m is None else (m != 0).astype(np.int64)
+            ss = ef_state.sufficient_statistics(x[:, c0:c0 + d], d)
+            last[i]["xis"] = fin[:, 0].cpu().numpy()
+            if T:
+                last[i]["mean"] = x[-1, c0:c0 + d] if d > 1 else x[-1, c0]
+                last[i]["observation_ss"] = ss[-1]
+                last[i]["observed"] = seen[-1]
+            if record_trajectories:
+                nt[i] = {"dimension": np.full(T, d), "nus": np.full(T, a["nus"], dtype=cast), "xis": traj[:, :, 0].t().cpu().numpy(),
+                         "observed": seen, "mean": x[:, c0:c0 + d] if d > 1 else x[:, c0], "observation_ss": ss}
+        last[-1]["time_step"] = float(ts[-1]) if T else 0.0
+        self.last_attributes = last
+        if record_trajectories:
+            nt[-1] = {"time_step": ts.astype(cast),
+                      "precision_clipping_value": np.full(T, self.attributes[-1]["precision_clipping_value"], dtype=cast)}
+            self.node_trajectories = nt
+        else:
+            self.node_trajectories = None
+        self._last_inputs = (input_data, time_steps, observed)
+        return self
+
+    def _ef_batch(self, input_data, parameters, observed, n_instances, input_group_size, record, last_attributes):
+        """``batch`` for an ef-state network: instances differ in ``(node, "nus")`` and, with groups, in their series."""
+        dev = self.device
+        dt = _torch_dtype(self.bits)
+        grouped = input_group_size > 0
+        x = torch.as_tensor(np.asarray(input_data) if not torch.is_tensor(input_data) else input_data).to(device=dev, dtype=dt)
+        if not grouped:
+            x = x[:, None] if x.ndim == 1 else x
+            x = x[None]
+        elif x.ndim == 2:
+            x = x[:, :, None]
+        cols = self._ef_columns(x.shape[2])
+        for k in parameters:
+            if not (isinstance(k, (tuple, list)) and len(k) == 2 and k[1] == "nus" and self.edges[k[0]].node_type == ef_state.NODE_TYPE):
+                raise ValueError(f"unknown parameter {k!r}: an ef-state network takes (node, 'nus')")
+        if n_instances is None:
+            sizes = {int(v.numel()) if torch.is_tensor(v) else int(np.size(v)) for v in parameters.values()} - {1}
+            if len(sizes) > 1:
+                raise ValueError(f"per-instance parameters disagree on the batch size: {sorted(sizes)}")
+            n_instances = sizes.pop() if sizes else (x.shape[0] * input_group_size if grouped else 1)
+        if grouped and x.shape[0] * input_group_size < n_instances:
+            raise ValueError("not enough input series for n_instances / input_group_size")
+        obs = None
+        if observed is not None:
+            obs = torch.as_tensor(np.asarray(observed) if not torch.is_tensor(observed) else observed).to(dev)
+            obs = obs.reshape(x.shape[0], x.shape[1], -1)
+        wanted = {tuple(k) for k in record}
+        if any(k[1] != "xis" for k in wanted):
+            raise ValueError("an ef-state network records (node, 'xis')")
+        res = BatchResult()
+        res.n_instances = n_instances
+        res.trajectories, lasts = {}, {}
+        for j, (i, c0, d) in enumerate(cols):
+            v = parameters.get((i, "nus"), self.attributes[i]["nus"])
+            nus = torch.as_tensor(v).to(device=dev, dtype=dt).reshape(-1)
+            nus = nus.expand(n_instances).contiguous() if nus.numel() == 1 else nus.contiguous()
+            m = None if obs is None else (obs[:, :, min(j, obs.shape[2] - 1)] != 0).to(torch.uint8).contiguous()
+            traj, fin = ef_state.launch(bits=self.bits, device=dev, series=x[:, :, c0:c0 + d].contiguous(), observed=m, nus=nus,
+                                        xis0=self.attributes[i]["xis"], dimension=d, input_group_size=input_group_size,
+                                        want_trajectory=(i, "xis") in wanted)
+            if traj is not None:
+                res.trajectories[(i, "xis")] = traj.permute(2, 1, 0)  # [N][T][K] view of the kernel's [K][T][N]
+            lasts[(i, "xis")] = fin.t()
+        res.last_attributes = lasts if last_attributes else None
+        return res
 
     def _unflatten(self, vec: np.ndarray, time_step: float) -> dict:
         out = deepcopy(self.attributes)
@@ -882,6 +1024,10 @@ class Network:
         parameters = dict(parameters or {})
         if self.scan_fn is None:
             self.create_belief_propagation_fn()
+        if self._ef_nodes():
+            if response_function is not None or gradient or pointwise or fused_reduce is not None or time_steps is not None:
+                raise NotImplementedError("an ef-state network has no response function, gradient or time steps on this path")
+            return self._ef_batch(input_data, parameters, observed, n_instances, input_group_size, record, last_attributes)
         dev = self.device
         split = self._split_over_components(input_data, parameters, response_function, response_function_inputs,
                                             response_function_parameters, time_steps, observed, n_instances, input_group_size,

@@ -893,3 +893,80 @@ def test_disconnected_network_is_split_over_components(G, monkeypatch):
         assert torch.allclose(a, b, rtol=1e-6, atol=1e-7, equal_nan=True), k
     # a connected network, a call with a response function or a gradient are not split
     assert nets.binary3(G.Network).connected_components() == [[0, 1, 2]]
+
+
+# ---------------------------------------------------------------- ef-state nodes (hgf_ef_filter)
+def test_ef_state_reference_golden(G):
+    """tests/test_nodes/test_exponential_family.py:14-66 through the drop-in surface: same calls, same golden."""
+    from oracle import ef_state as ef
+
+    x = ef.spiral_data()
+    uni = G.Network().add_nodes(kind="ef-state", learning="generalised-filtering").input_data(input_data=x[:, 0])
+    assert np.isfinite(uni.node_trajectories[0]["xis"]).all() and uni.node_trajectories[0]["xis"].shape == (1000, 2)
+    net = G.Network().add_nodes(kind="ef-state", nus=3.0, learning="generalised-filtering",
+                                distribution="multivariate-normal", dimension=2).input_data(input_data=x)
+    golden = np.array([3.4652710e01, -1.0609777e00, 1.2103647e03, -3.6398651e01, 3.3951855e00], dtype=np.float32)
+    got = net.node_trajectories[0]["xis"]
+    assert got.dtype == np.float32 and np.isclose(got[-1], golden).all()
+    want = ef.ef_filter(x, 3.0, 2, "multivariate-normal")
+    assert np.allclose(got, want, rtol=RTOL_TRAJ, atol=1e-6)
+    assert np.allclose(net.last_attributes[0]["xis"], want[-1], rtol=RTOL_TRAJ, atol=1e-6)
+    assert np.allclose(net.node_trajectories[0]["observation_ss"][7], ef.sufficient_statistics(x[7], 2), rtol=1e-6)
+    assert np.allclose(net.node_trajectories[0]["mean"], x.astype(np.float32))
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+@pytest.mark.parametrize("d", [1, 2, 3, 5, 8])
+def test_ef_state_batch_matches_oracle(G, d, bits):
+    """Instances that differ in nus and in their series, with unobserved steps, every built dimension."""
+    import torch
+    from oracle import ef_state as ef
+
+    rng = np.random.default_rng(40 + d)
+    dtype, name = (np.float32, "float32") if bits == 32 else (np.float64, "float64")
+    Gs, g, T = 3, 67, 41  # 201 instances: not a multiple of the block size
+    x = rng.normal(0.5, 2.0, size=(Gs, T, d))
+    mask = rng.random((Gs, T)) > 0.2
+    nus = rng.uniform(0.5, 20.0, Gs * g)
+    dist = "normal" if d == 1 else "multivariate-normal"
+    net = G.Network(dtype=name).add_nodes(kind="ef-state", dimension=d, distribution=dist)
+    r = net.batch(x, {(0, "nus"): nus}, observed=mask, input_group_size=g, record=[(0, "xis")], last_attributes=True)
+    traj = r.trajectories[(0, "xis")].cpu().numpy()
+    last = r.last_attributes[(0, "xis")].cpu().numpy()
+    K = d + d * (d + 1) // 2
+    assert traj.shape == (Gs * g, T, K) and last.shape == (Gs * g, K)
+    rtol = RTOL_TRAJ if bits == 32 else 1e-12
+    for n in (0, 1, 66, 67, 130, 200):
+        want = ef.ef_filter(x[n // g], dtype(nus[n]), d, dist, observed=mask[n // g], dtype=dtype)
+        assert np.allclose(traj[n], want, rtol=rtol, atol=rtol), (n, np.abs(traj[n] - want).max())
+        assert np.array_equal(last[n], traj[n, -1])
+    # a shared series, no mask, no trajectory: only the final statistics come back
+    r2 = net.batch(x[0], {(0, "nus"): nus[:50]}, last_attributes=True)
+    assert r2.trajectories == {}
+    want = ef.ef_filter(x[0], dtype(nus[7]), d, dist, dtype=dtype)
+    assert np.allclose(r2.last_attributes[(0, "xis")][7].cpu().numpy(), want[-1], rtol=rtol, atol=rtol)
+    assert torch.cuda.is_available()
+
+
+def test_ef_state_two_input_nodes_and_errors(G):
+    from oracle import ef_state as ef
+    from pyhgf_b200 import _lib
+
+    rng = np.random.default_rng(5)
+    x = rng.normal(size=(30, 3))
+    net = (G.Network().add_nodes(kind="ef-state", nus=2.0)
+           .add_nodes(kind="ef-state", nus=9.0, dimension=2, distribution="multivariate-normal"))
+    before = _lib.launch_count()
+    net.input_data(x)
+    assert _lib.launch_count() - before == 2  # one launch per node
+    assert np.allclose(net.node_trajectories[0]["xis"], ef.ef_filter(x[:, 0], 2.0, 1, "normal"), rtol=RTOL_TRAJ, atol=1e-6)
+    assert np.allclose(net.node_trajectories[1]["xis"], ef.ef_filter(x[:, 1:], 9.0, 2, "multivariate-normal"), rtol=RTOL_TRAJ, atol=1e-6)
+    with pytest.raises(ValueError, match="column"):
+        net.input_data(x[:, :2])
+    c = _lib.EfCall()
+    c.dtype, c.n_instances, c.n_steps, c.dimension = 32, 4, 3, 9
+    assert _lib.lib().hgf_ef_filter(C.byref(c), None) != 0 and b"dimension" in _lib.lib().hgf_last_error()
+    c.dimension = 2
+    assert _lib.lib().hgf_ef_filter(C.byref(c), None) != 0 and b"null input" in _lib.lib().hgf_last_error()
+    c.n_instances = 0
+    assert _lib.lib().hgf_ef_filter(C.byref(c), None) == 0  # empty batch: nothing to do

@@ -46,6 +46,31 @@ def test_struct_layouts_match_the_header(lib):
 
     assert fields("hgf_topology_t") == [f[0] for f in lib.Topology._fields_]
     assert fields("hgf_call_t") == [f[0] for f in lib.Call._fields_]
+    assert fields("hgf_ef_call_t") == [f[0] for f in lib.EfCall._fields_]
+
+
+def test_ef_state_node_defaults(lib):
+    """add_ef_state, pyhgf/model/add_nodes.py:360-470: defaults, derived entries, the keys it pops, its errors."""
+    from pyhgf_b200.network import Network
+
+    n = Network().add_nodes(kind="ef-state")
+    a = n.attributes[0]
+    assert n.edges[0].node_type == 3 and a["nus"] == 3.0 and a["dimension"] == 1 and a["observed"] == 1
+    assert np.array_equal(a["xis"], [0.0, 1.0]) and a["mean"] == 0.0 and a["observation_ss"].shape == (2,)
+    assert "distribution" not in a and "learning" not in a
+    m = Network().add_nodes(kind="ef-state", nus=5.0, dimension=2, distribution="multivariate-normal")
+    assert np.array_equal(m.attributes[0]["xis"], [0, 0, 1, 0, 1]) and m.attributes[0]["observation_ss"].shape == (5,)
+    m.create_belief_propagation_fn()
+    assert m.input_idxs == (0,) and m.input_dim == [2]
+    with pytest.raises(ValueError, match="either 'normal' or 'multivariate-normal'"):
+        Network().add_nodes(kind="ef-state", distribution="gamma")
+    with pytest.raises(NotImplementedError, match="generalised-filtering"):
+        Network().add_nodes(kind="ef-state", learning="hgf-2")
+    with pytest.raises(ValueError, match="not found in the default"):
+        Network().add_nodes(kind="ef-state", tonic_volatility=-2.0)
+    mixed = Network().add_nodes(kind="ef-state").add_nodes()
+    with pytest.raises(NotImplementedError, match="two networks"):
+        mixed.create_belief_propagation_fn()
 
 
 BUILDERS = [nets.binary3, nets.binary2, nets.continuous2, nets.continuous3, nets.nonlinear, nets.tanh_coupling,
@@ -99,7 +124,7 @@ def test_api_errors_match_the_reference(lib):
     with pytest.raises(ValueError, match="coupling fn and value children do not match"):
         Network().add_nodes(n_nodes=3).add_nodes(value_children=[0, 1, 2], coupling_fn=(None, None))
     with pytest.raises(NotImplementedError):
-        Network().add_nodes(kind="ef-state")
+        Network().add_nodes(kind="categorical-state")
     net = Network().add_nodes().add_nodes(value_children=0)
     assert net.input_idxs == (0,)
     assert net.attributes[0]["autoconnection_strength"] == 0.0 and net.attributes[0]["tonic_volatility"] == 0.0

@@ -452,3 +452,26 @@ def test_oracle_reproduces_the_committed_vectors():
     slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
     s, g = o.batch_grad(d["binary_u"], slots, v["config4/params"], "binary_softmax_inverse_temperature", resp_inputs=d["binary_y"])
     assert np.allclose(s, v["config4/surprise"], rtol=1e-12) and np.allclose(g, v["config4/gradient"], rtol=1e-9)
+
+
+def test_exponential_family_fixed_learning_rate_golden():
+    """tests/test_nodes/test_exponential_family.py:14-66: the univariate run has no NaN, the bivariate spiral ends at
+    the xis the reference asserts."""
+    from oracle import ef_state as ef
+
+    x = ef.spiral_data()
+    tr = ef.ef_filter(x, 3.0, 2, "multivariate-normal")
+    golden = np.array([3.4652710e01, -1.0609777e00, 1.2103647e03, -3.6398651e01, 3.3951855e00], dtype=np.float32)
+    assert np.isclose(tr[-1], golden).all()
+    uni = ef.ef_filter(x[:, 0], 3.0, 1, "normal")
+    assert uni.shape == (1000, 2) and np.isfinite(uni).all()
+    # the update is an exponential moving average of t(x) with weight 1/(1+nu): closed form after T steps
+    w = 1.0 / 4.0
+    t = np.stack([x[:, 0], x[:, 0] ** 2], 1)
+    k = np.arange(len(x))[::-1]
+    closed = (w * (1 - w) ** k)[:, None] * t
+    expected = closed.sum(0) + (1 - w) ** len(x) * np.array([0.0, 1.0])
+    assert np.allclose(ef.ef_filter(x[:, 0], 3.0, 1, "normal", dtype=np.float64)[-1], expected, rtol=1e-12)
+    mask = (np.arange(len(x)) % 3 != 0)
+    held = ef.ef_filter(x, 3.0, 2, "multivariate-normal", observed=mask)
+    assert np.array_equal(held[3], held[2]) and not np.array_equal(held[4], held[3])
