@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define HGF_ABI_VERSION 3
+#define HGF_ABI_VERSION 4
 
 /* number of scalar attribute fields per node, and their order (slot = node * HGF_N_FIELDS + field).
  * Names are the reference's attribute keys, pyhgf/model/add_nodes.py:65-85, 159-184, 330-340. */
@@ -60,7 +60,17 @@ typedef struct {
   int32_t volatility_updates;             /* 0 unbounded, 1 eHGF, 2 standard */
   int32_t mean_field_updates;
   double max_posterior_precision;
+  /* Switching plans -- Network.input_custom_sequence (pyhgf/model/network.py:653-767: lax.switch over several update
+   * sequences, one branch index per step).  n_branches <= 1: one schedule, as above.  Otherwise prediction_* /
+   * update_* hold the branches' steps back to back (n_prediction_steps / n_update_steps are the totals) and branch b
+   * owns steps [branch_prediction_ptr[b], branch_prediction_ptr[b+1]) and [branch_update_ptr[b], branch_update_ptr[b+1]).
+   * At most HGF_MAX_BRANCHES; such a plan runs through the opcode interpreter and needs hgf_call_t::branch_idx. */
+  int32_t n_branches;
+  const int32_t* branch_prediction_ptr;   /* [n_branches + 1] */
+  const int32_t* branch_update_ptr;       /* [n_branches + 1] */
 } hgf_topology_t;
+
+#define HGF_MAX_BRANCHES 8
 
 enum hgf_coupling_fn { HGF_CF_LINEAR = 0, HGF_CF_IDENTITY = 1, HGF_CF_RELU = 2, HGF_CF_SIGMOID = 3, HGF_CF_TANH = 4,
                        HGF_CF_LEAKY_RELU = 5, HGF_CF_GELU = 6, HGF_CF_SIN = 7 };
@@ -130,6 +140,9 @@ typedef struct {
    * the reference's n_predictions.  input_data / observed are ignored; hgf_filter only. */
   int32_t generative;
   uint64_t seed;
+  /* Switching plans only: the branch taken at each step, [T] (shared by the instances; out-of-range values are clamped
+   * like lax.switch).  Device pointer for hgf_filter / hgf_logp_grad, host pointer for the *_host entry points. */
+  const int32_t* branch_idx;
 } hgf_call_t;
 
 int hgf_abi_version(void);

@@ -585,6 +585,61 @@ class Network:
                               _dp(slots0), _dp(ri), _dp(out))
         return out
 
+    # -- Network.input_custom_sequence -- network.py:653-767 ---------------------
+    def _set_schedule(self, seq):
+        pred, upd = seq
+        pn = np.asarray([s[0] for s in pred] or [0], dtype=np.int32)
+        po = np.asarray([s[1] for s in pred] or [0], dtype=np.int32)
+        un = np.asarray([s[0] for s in upd] or [0], dtype=np.int32)
+        uo = np.asarray([s[1] for s in upd] or [0], dtype=np.int32)
+        lib().oracle_net_set_schedule(self._handle, len(pred), _ip(pn), _ip(po), len(upd), _ip(un), _ip(uo))
+
+    def input_custom_sequence(self, update_branches, branches_idx, input_data, time_steps=None, observed=None):
+        """``lax.switch(idx, branches_fn, attributes, data)`` under ``scan`` (network.py:746-758): every step runs the
+        belief propagation of the branch its index names (clamped, as lax.switch does).  Runs of equal index are
+        filtered with that branch's schedule, the attribute vector carried from one run to the next."""
+        if self._handle is None:
+            self.create_belief_propagation_fn()
+        x, ts, obs, n_steps = self._format_inputs(input_data, time_steps, observed)
+        n_fed = x.shape[1]
+        if n_fed != self._n_fed:
+            ii = np.asarray(self.input_idxs, dtype=np.int32)
+            lib().oracle_net_set_inputs(self._handle, len(ii), _ip(ii), n_fed)
+            self._n_fed = n_fed
+        idx = np.clip(np.asarray(branches_idx, dtype=np.int64), 0, len(update_branches) - 1)
+        assert idx.shape == (n_steps,)
+        slots = self.flatten()
+        traj = np.zeros((n_steps, len(self.edges) * NF), dtype=np.float64)
+        t0 = 0
+        while t0 < n_steps:
+            t1 = t0 + 1
+            while t1 < n_steps and idx[t1] == idx[t0]:
+                t1 += 1
+            self._set_schedule(update_branches[idx[t0]])
+            seg = np.zeros((t1 - t0, traj.shape[1]), dtype=np.float64)
+            lib().oracle_run(self._handle, self.dtype, t1 - t0, _dp(np.ascontiguousarray(x[t0:t1])),
+                             _dp(None if obs is None else np.ascontiguousarray(obs[t0:t1])),
+                             _dp(None if ts is None else np.ascontiguousarray(ts[t0:t1])), _dp(slots), _dp(seg))
+            traj[t0:t1] = seg
+            t0 = t1
+        self._set_schedule(self.update_sequence)
+        self.last_attributes = self.unflatten(slots, 1.0 if ts is None else ts[-1])
+        nt = {}
+        for i in range(len(self.edges)):
+            d, temp = {}, {}
+            for k, name in enumerate(FIELDS):
+                col = traj[:, i * NF + k]
+                if name.startswith("temp."):
+                    if name[5:] in self.attributes[i].get("temp", {}):
+                        temp[name[5:]] = col
+                elif name in self.attributes[i]:
+                    d[name] = col
+            d["temp"] = temp
+            nt[i] = d
+        nt[-1] = {"time_step": np.ones(n_steps) if ts is None else ts}
+        self.node_trajectories = nt
+        return self
+
     def apply_op(self, op: str, node: int, attributes: dict, time_step: Optional[float] = None) -> dict:
         """Run one update step on an attributes dict (isolated-kernel goldens)."""
         if self._handle is None:

@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libpyhgf_cuda_accurate.so" if os.environ.
 N_FIELDS = 19
 N_RESPONSE_PARAMETERS = 4
 MAX_PARAMS = 16
+MAX_BRANCHES = 8  # HGF_MAX_BRANCHES
 MAX_RECORDS = 640
 
 #: order of the per-node attribute fields inside an instance's attribute vector
@@ -64,6 +65,7 @@ class Topology(C.Structure):
         ("n_inputs", C.c_int32), ("input_idxs", _i32p), ("n_fed", C.c_int32),
         ("volatility_updates", C.c_int32), ("mean_field_updates", C.c_int32),
         ("max_posterior_precision", C.c_double),
+        ("n_branches", C.c_int32), ("branch_prediction_ptr", _i32p), ("branch_update_ptr", _i32p),
     ]
 
 
@@ -103,6 +105,7 @@ class Call(C.Structure):
         ("multicast_workspace", C.c_void_p),
         ("generative", C.c_int32),
         ("seed", C.c_uint64),
+        ("branch_idx", C.c_void_p),
     ]
 
 
@@ -182,7 +185,7 @@ def lib() -> C.CDLL:
     L.hgf_fused_reduce_bytes.restype = C.c_int64
     L.hgf_fused_reduce_result_offset.argtypes = [C.c_int32, C.c_int32, C.c_uint32]
     L.hgf_fused_reduce_result_offset.restype = C.c_int64
-    if L.hgf_abi_version() != 3:
+    if L.hgf_abi_version() != 4:
         raise ImportError("libpyhgf_cuda.so ABI version mismatch; rebuild with `python -m pyhgf_b200.build --force`")
     _lib = L
     return L

@@ -79,6 +79,21 @@ int hgf_plan_create(const hgf_topology_t* t, hgf_plan_t** out) {
   p.vol_updates = t->volatility_updates;
   p.mean_field = t->mean_field_updates ? 1 : 0;
   p.max_posterior_precision = t->max_posterior_precision;
+  p.n_branches = t->n_branches > 1 ? t->n_branches : 0;
+  if (p.n_branches > MAX_BRANCHES) { delete plan; return fail("hgf_plan_create: %d branches (max %d)", t->n_branches, MAX_BRANCHES); }
+  if (p.n_branches) {
+    if (!t->branch_prediction_ptr || !t->branch_update_ptr) { delete plan; return fail("hgf_plan_create: branch pointers are null"); }
+    for (int b = 0; b <= p.n_branches; ++b) {
+      const int lo = b ? t->branch_prediction_ptr[b - 1] : 0, ulo = b ? t->branch_update_ptr[b - 1] : 0;
+      if (t->branch_prediction_ptr[b] < lo || t->branch_prediction_ptr[b] > p.n_pred || t->branch_update_ptr[b] < ulo || t->branch_update_ptr[b] > p.n_upd ||
+          (b == 0 && (t->branch_prediction_ptr[0] != 0 || t->branch_update_ptr[0] != 0))) {
+        delete plan;
+        return fail("hgf_plan_create: branch %d has a bad step range", b);
+      }
+      p.br_pred[b] = static_cast<uint8_t>(t->branch_prediction_ptr[b]);
+      p.br_upd[b] = static_cast<uint8_t>(t->branch_update_ptr[b]);
+    }
+  }
 
   auto fill = [&](const int32_t* ptr, const int32_t* idx, uint8_t* count, uint8_t* off, uint8_t* dst, const char* what) -> int {
     if (!ptr) return fail("hgf_plan_create: %s_ptr is null", what);
@@ -152,7 +167,7 @@ int hgf_plan_create(const hgf_topology_t* t, hgf_plan_t** out) {
   p.slot_clip = off++;
   p.slot_resp = off; off += N_RESP_PARAMS;
   p.n_slots = off;
-  plan->variant = select_variant(p);
+  plan->variant = p.n_branches ? &kInterpreterVariant : select_variant(p);  // switching needs the rolled schedule
   if (!plan->variant->matches && p.n_slots > INTERP_SLOTS) {
     delete plan;
     return fail("hgf_plan_create: network needs %d attribute slots; the interpreter holds %d", off, INTERP_SLOTS);
@@ -215,6 +230,9 @@ static int check_call(const hgf_plan_t* plan, const hgf_call_t* c, bool want_gra
     return fail("response function %d needs response_inputs", c->response_fn);
   if ((c->response_fn == RESP_FIRST_LEVEL_GAUSSIAN) && p.n_nodes < 2) return fail("first_level_gaussian_surprise needs a node 1");
   if (c->input_group_size < 0 || c->response_group_size < 0) return fail("negative group size");
+  if (p.n_branches && c->n_steps > 0 && !c->branch_idx) return fail("a switching plan needs branch_idx");
+  if (!p.n_branches && c->branch_idx) return fail("branch_idx given, but the plan has a single update sequence");
+  if (p.n_branches && c->generative) return fail("generative mode does not take a switching plan");
   if (c->world_size > 1) {
     if (c->world_size > MAX_PEERS) return fail("world_size=%d; the fused reduction spans at most %d GPUs", c->world_size, MAX_PEERS);
     if (c->rank < 0 || c->rank >= c->world_size) return fail("rank %d outside [0, %d)", c->rank, c->world_size);
@@ -299,6 +317,7 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
   a.input_data = c->input_data;
   a.observed = c->observed;
   a.time_steps = c->time_steps;
+  a.branch_idx = plan->prog.n_branches ? c->branch_idx : nullptr;
   a.attributes = c->attributes;
   a.params = c->params;
   a.response_inputs = c->response_inputs;
@@ -434,7 +453,7 @@ static int run_host_chunked(const hgf_plan_t* plan, const hgf_call_t* c, bool wa
   if (env && env[0] == '0') return -1;
   const Program& p = plan->prog;
   const long long N = c->n_instances;
-  if (N < 32768 || c->trajectories || c->surprise_pointwise || c->last_attributes || c->world_size > 1 || c->generative) return -1;
+  if (N < 32768 || c->trajectories || c->surprise_pointwise || c->last_attributes || c->world_size > 1 || c->generative || c->branch_idx) return -1;
   if (!c->surprise_sum && !c->gradient) return -1;
   auto lcm = [](long long a, long long b) { long long x = a, y = b; while (y) { long long t = x % y; x = y; y = t; } return a / x * b; };
   long long unit = 64;
@@ -540,7 +559,8 @@ static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, boo
   const size_t sz_traj = static_cast<size_t>(lists.n_rec) * T * N * w, sz_last = static_cast<size_t>(p.n_nodes) * NF * N * w;
   const size_t sz_sum = N * w, sz_pw = T * N * w, sz_grad = sz_par, sz_red = static_cast<size_t>(n_groups) * w;
   auto need = [](const void* ptr, size_t b) { return ptr && b ? aligned(b) : size_t(0); };
-  const size_t total = need(c->input_data, sz_in) + need(c->observed, sz_obs) + need(c->time_steps, sz_ts) + need(c->attributes, sz_attr) +
+  const size_t sz_br = T * sizeof(int32_t);
+  const size_t total = need(c->branch_idx, sz_br) + need(c->input_data, sz_in) + need(c->observed, sz_obs) + need(c->time_steps, sz_ts) + need(c->attributes, sz_attr) +
                        need(c->params, sz_par) + need(c->response_inputs, sz_resp) + need(c->group, sz_group) + need(c->trajectories, sz_traj) +
                        need(c->last_attributes, sz_last) + need(c->surprise_sum, sz_sum) + need(c->surprise_pointwise, sz_pw) +
                        (want_grad ? need(c->gradient, sz_grad) : 0) + need(c->reduced, sz_red);
@@ -553,6 +573,7 @@ static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, boo
   d.input_data = st.in(c->input_data, sz_in);
   d.observed = static_cast<const uint8_t*>(st.in(c->observed, sz_obs));
   d.time_steps = st.in(c->time_steps, sz_ts);
+  d.branch_idx = static_cast<const int32_t*>(st.in(c->branch_idx, sz_br));
   d.attributes = st.in(c->attributes, sz_attr);
   d.params = st.in(c->params, sz_par);
   d.response_inputs = st.in(c->response_inputs, sz_resp);

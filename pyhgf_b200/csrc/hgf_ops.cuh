@@ -27,6 +27,9 @@ struct RuntimeTopo {
   HGF_D int n_upd() const { return p.n_upd; }
   HGF_D int upd_node(int i) const { return p.upd_node[i]; }
   HGF_D int upd_op(int i) const { return p.upd_op[i]; }
+  HGF_D int n_branches() const { return p.n_branches; }
+  HGF_D int br_pred(int b) const { return p.br_pred[b]; }
+  HGF_D int br_upd(int b) const { return p.br_upd[b]; }
   HGF_D int n_inputs() const { return p.n_inputs; }
   HGF_D int n_fed() const { return p.n_fed; }
   HGF_D int input_idx(int k) const { return p.input_idx[k]; }

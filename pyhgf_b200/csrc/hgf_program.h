@@ -9,7 +9,8 @@ namespace hgf {
 
 constexpr int MAX_NODES = 32;
 constexpr int MAX_EDGES = 96;     // per edge kind
-constexpr int MAX_STEPS = 96;     // prediction steps / update steps
+constexpr int MAX_STEPS = 96;     // prediction steps / update steps (summed over the branches of a switching plan)
+constexpr int MAX_BRANCHES = 8;   // update-sequence branches of input_custom_sequence
 constexpr int MAX_INPUTS = 16;
 constexpr int MAX_RECORDS = 640;  // recorded (node, field) leaves
 constexpr int MAX_PARAMS = 16;    // batched (per-instance) parameters
@@ -76,6 +77,10 @@ struct Program {
   uint8_t pred_node[MAX_STEPS], pred_op[MAX_STEPS];
   uint8_t upd_node[MAX_STEPS], upd_op[MAX_STEPS];
   uint8_t input_idx[MAX_INPUTS];
+  // input_custom_sequence (network.py:653-767): branch b's steps are pred_*[br_pred[b] .. br_pred[b+1]) and
+  // upd_*[br_upd[b] .. br_upd[b+1]); n_branches <= 1 is the ordinary single schedule (n_pred / n_upd)
+  int32_t n_branches;
+  uint8_t br_pred[MAX_BRANCHES + 1], br_upd[MAX_BRANCHES + 1];
 };
 
 // Per-call lists (which leaves are recorded, which slots are per-instance).
@@ -111,6 +116,7 @@ struct ScanArgs {
   const void* input_data;
   const uint8_t* observed;
   const void* time_steps;
+  const int32_t* branch_idx;  // [T] branch taken at each step (switching plans only)
   const void* attributes;
   const void* params;
   const void* response_inputs;

@@ -161,10 +161,17 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
       st.log_dt = x_log(st.dt);
     }
     // prediction sequence (parents before children)
+    [[maybe_unused]] int pred_lo = 0, pred_hi = a.n_pred(), upd_lo = 0, upd_hi = a.n_upd();
     if constexpr (Topo::is_static) {
       a.run_predictions(s, st);
     } else {
-      for (int i = 0; i < a.n_pred(); ++i) apply_op(a, s, st, a.pred_op(i), a.pred_node(i));
+      // a switching plan (input_custom_sequence, network.py:746-758) picks this step's branch; lax.switch clamps
+      if (args.branch_idx) {
+        int b = HGF_LDG(args.branch_idx + t);
+        b = b < 0 ? 0 : (b >= a.n_branches() ? a.n_branches() - 1 : b);
+        pred_lo = a.br_pred(b), pred_hi = a.br_pred(b + 1), upd_lo = a.br_upd(b), upd_hi = a.br_upd(b + 1);
+      }
+      for (int i = pred_lo; i < pred_hi; ++i) apply_op(a, s, st, a.pred_op(i), a.pred_node(i));
     }
     // set_observation, pyhgf/updates/observation.py:10-38
     if (REC && args.generative) {  // rollouts always record: only the recording kernels carry this branch
@@ -195,7 +202,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
     if constexpr (Topo::is_static) {
       a.run_updates(s, st);
     } else {
-      for (int i = 0; i < a.n_upd(); ++i) apply_op(a, s, st, a.upd_op(i), a.upd_node(i));
+      for (int i = upd_lo; i < upd_hi; ++i) apply_op(a, s, st, a.upd_op(i), a.upd_node(i));
     }
 
     if (response_fn != RESP_NONE) {

@@ -540,12 +540,12 @@ class Network:
     def _launch(self, *, values, observed, time_steps, input_group_size, n_instances, params: dict,
                 response_fn: int, response_inputs, response_group_size, response_parameters, record_slots,
                 want_last, want_sum, want_pointwise, want_grad, group, n_groups, out_scale=1.0, stream=None,
-                attributes=None, fused_reduce=None, generative_seed=None):
+                attributes=None, fused_reduce=None, generative_seed=None, plan=None, branch_idx=None):
         L = _lib.lib()
         dev = values.device
         dt = _torch_dtype(self.bits)
         n_fed = values.shape[2]
-        plan = self._get_plan(n_fed)
+        plan = self._get_plan(n_fed) if plan is None else plan
         T = int(values.shape[1])
         N = int(n_instances)
         keep = [values]
@@ -565,6 +565,12 @@ class Network:
                 raise ValueError("time_steps should have one entry per observation")
             keep.append(ts)
             call.time_steps = ts.data_ptr()
+        if branch_idx is not None:
+            br = torch.as_tensor(np.asarray(branch_idx, dtype=np.int32)).to(dev).contiguous()
+            if br.numel() != T:
+                raise ValueError("branches_idx should have one entry per observation")
+            keep.append(br)
+            call.branch_idx = br.data_ptr()
         attr = torch.from_numpy(self._flatten(plan, attributes, response_parameters)).to(dev)
         keep.append(attr)
         call.attributes = attr.data_ptr()
@@ -675,15 +681,55 @@ class Network:
             self.create_belief_propagation_fn()
         if self._ef_nodes():
             return self._ef_input_data(input_data, time_steps, observed, record_trajectories)
+        self._filter_one_series(input_data, time_steps, observed, record_trajectories)
+        self._last_inputs = (input_data, time_steps, observed)
+        return self
+
+    def input_custom_sequence(self, update_branches, branches_idx, input_data, time_steps=None, observed=None,
+                              input_idxs=None, rng_keys=None):
+        """Filter one series with an update sequence chosen per observation (network.py:653-767): step ``t`` runs
+        ``update_branches[branches_idx[t]]`` (``lax.switch`` in the reference, the interpreter's branch table here).
+
+        ``update_branches`` are ``UpdateSequence``s over this network's nodes -- e.g. ``self.update_sequence`` with some
+        steps removed; every step's function must be one of ``pyhgf_b200.topology``'s update functions.
+        """
+        if rng_keys is not None:
+            raise NotImplementedError("rng_keys only serve action functions, which are outside the accelerated path")
+        if input_idxs is not None:
+            self.input_idxs = input_idxs
+        if self.scan_fn is None:
+            self.create_belief_propagation_fn()
+        if self._ef_nodes():
+            raise NotImplementedError("an ef-state network has a single one-step update sequence")
+        branches = tuple((tuple(b[0]), tuple(b[1])) for b in update_branches)
+        if not 1 <= len(branches) <= _lib.MAX_BRANCHES:
+            raise ValueError(f"between 1 and {_lib.MAX_BRANCHES} update branches, got {len(branches)}")
+        for b in branches:
+            for _, fn in b[0] + b[1]:
+                if not hasattr(fn, "opcode"):
+                    raise NotImplementedError("custom update functions cannot cross the C ABI: build the branches from "
+                                              "the steps of Network.update_sequence")
+        self._filter_one_series(input_data, time_steps, observed, True, branches=branches, branches_idx=branches_idx)
+        return self
+
+    def _filter_one_series(self, input_data, time_steps, observed, record_trajectories, branches=None, branches_idx=None):
         dev = self.device
         values, obs = self._format_series(input_data, observed, dev, grouped=False)
         plan = self._get_plan(values.shape[2])
+        if branches is not None and len(branches) == 1:
+            plan = Plan(self.edges, branches[0], self.input_idxs, values.shape[2], self.volatility_updates,
+                        self.mean_field_updates, self.max_posterior_precision)
+            branches_idx = None
+        elif branches is not None:
+            plan = Plan(self.edges, branches[0], self.input_idxs, values.shape[2], self.volatility_updates,
+                        self.mean_field_updates, self.max_posterior_precision, branches=branches)
         T = values.shape[1]
         record = list(range(self.n_nodes * _lib.N_FIELDS)) if record_trajectories else []
         res, plan = self._launch(values=values, observed=obs, time_steps=time_steps, input_group_size=0, n_instances=1,
                                  params={}, response_fn=0, response_inputs=None, response_group_size=0,
                                  response_parameters=None, record_slots=record, want_last=True, want_sum=False,
-                                 want_pointwise=False, want_grad=False, group=None, n_groups=0)
+                                 want_pointwise=False, want_grad=False, group=None, n_groups=0, plan=plan,
+                                 branch_idx=branches_idx)
         last = res._last[:, 0].double().cpu().numpy()
         ts = np.ones(T) if time_steps is None else np.asarray(time_steps, dtype=np.float64)
         self.last_attributes = self._unflatten(last, float(ts[-1]) if T else 0.0)
@@ -711,8 +757,6 @@ class Network:
             self.node_trajectories = nt
         else:
             self.node_trajectories = None
-        self._last_inputs = (input_data, time_steps, observed)
-        return self
 
     # ---------------------------------------------------- ef-state networks
     def _ef_columns(self, n_columns: int) -> list:

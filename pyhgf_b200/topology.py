@@ -151,7 +151,7 @@ class Plan:
     """A lowered network: owns the library's ``hgf_plan_t`` and knows the attribute-vector layout."""
 
     def __init__(self, edges, update_sequence: UpdateSequence, input_idxs, n_fed, volatility_updates, mean_field_updates,
-                 max_posterior_precision):
+                 max_posterior_precision, branches=None):
         L = _lib.lib()
         n = len(edges)
         self.n_nodes = n
@@ -176,6 +176,14 @@ class Plan:
                 fns.append(resolve_coupling_fn(e.coupling_fn[k] if k < len(e.coupling_fn) else None))
         arrays["value_children_fn"] = np.asarray(fns or [0], np.int32)
         pred, upd = update_sequence
+        self.n_branches = 0
+        if branches is not None and len(branches) > 1:
+            # input_custom_sequence (network.py:653-767): the branches' steps back to back, CSR pointers per branch
+            self.n_branches = len(branches)
+            pred = tuple(s for b in branches for s in b[0])
+            upd = tuple(s for b in branches for s in b[1])
+            arrays["branch_prediction_ptr"] = np.cumsum([0] + [len(b[0]) for b in branches]).astype(np.int32)
+            arrays["branch_update_ptr"] = np.cumsum([0] + [len(b[1]) for b in branches]).astype(np.int32)
         arrays["prediction_node"] = np.asarray([s[0] for s in pred] or [0], np.int32)
         arrays["prediction_op"] = np.asarray([s[1].opcode for s in pred] or [0], np.int32)
         arrays["update_node"] = np.asarray([s[0] for s in upd] or [0], np.int32)
@@ -186,6 +194,7 @@ class Plan:
         topo.n_nodes = n
         for key, arr in arrays.items():
             setattr(topo, key, arr.ctypes.data_as(C.POINTER(C.c_int32)))
+        topo.n_branches = self.n_branches
         topo.n_prediction_steps = len(pred)
         topo.n_update_steps = len(upd)
         topo.n_inputs = len(self.input_idxs)

@@ -970,3 +970,56 @@ def test_ef_state_two_input_nodes_and_errors(G):
     assert _lib.lib().hgf_ef_filter(C.byref(c), None) != 0 and b"null input" in _lib.lib().hgf_last_error()
     c.n_instances = 0
     assert _lib.lib().hgf_ef_filter(C.byref(c), None) == 0  # empty batch: nothing to do
+
+
+# ---------------------------------------------------------------- input_custom_sequence (switching plans)
+def test_custom_sequence_reference_case(G, datasets):
+    """tests/test_model.py:270-317: two copies of the network's own sequence, random branch indexes -- the result is
+    the plain filter's."""
+    u = datasets["u"]
+    net = nets.binary3(G.Network).create_belief_propagation_fn()
+    seq = net.update_sequence
+    idx = np.random.default_rng(3).binomial(1, 0.5, len(u))
+    net.scan_fn = None
+    net.input_custom_sequence(update_branches=(seq, seq), branches_idx=idx, input_data=u)
+    plain = nets.binary3(G.Network).input_data(u)
+    for node in range(3):
+        for k in ("mean", "precision", "expected_mean", "expected_precision"):
+            assert np.allclose(net.node_trajectories[node][k], plain.node_trajectories[node][k], rtol=RTOL_TRAJ, atol=1e-7, equal_nan=True)
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("build", [nets.binary3, nets.continuous3], ids=["binary3", "continuous3"])
+def test_custom_sequence_matches_oracle(G, datasets, build, dtype):
+    """Branches that drop the top level's update, or every update: trajectories vs the oracle's switching scan."""
+    rng = np.random.default_rng(11)
+    u = datasets["u"][:200] if build is nets.binary3 else datasets["x"][:200]
+    net = build(G.Network, dtype=dtype).create_belief_propagation_fn()
+    o = build(onet.Network, dtype=dtype).create_belief_propagation_fn()
+    top = len(net.edges) - 1
+    gseq, oseq = net.update_sequence, o.update_sequence
+    gb = (gseq, (gseq.prediction_steps, tuple(s for s in gseq.update_steps if s[0] != top)), (gseq.prediction_steps, ()))
+    ob = (oseq, (oseq[0], tuple(s for s in oseq[1] if s[0] != top)), (oseq[0], ()))
+    idx = rng.integers(-1, 4, len(u))  # out-of-range values are clamped, as lax.switch does
+    ts = rng.uniform(0.5, 2.0, len(u))
+    net.input_custom_sequence(gb, idx, u, time_steps=ts)
+    o.input_custom_sequence(ob, idx, u, time_steps=ts)
+    assert_traj_close(net, o, range(len(net.edges)), RTOL_TRAJ if dtype == "float32" else 1e-9)
+    assert np.isclose(net.last_attributes[top]["mean"], o.last_attributes[top]["mean"], rtol=1e-5)
+    # the top level really was frozen on the steps that skipped it
+    frozen = np.flatnonzero(np.clip(idx, 0, 2)[1:] == 2) + 1
+    assert np.array_equal(net.node_trajectories[top]["mean"][frozen], net.node_trajectories[top]["mean"][frozen - 1])
+
+
+def test_custom_sequence_abi_errors(G):
+    from pyhgf_b200 import _lib
+
+    net = nets.binary3(G.Network).create_belief_propagation_fn()
+    seq = net.update_sequence
+    with pytest.raises(ValueError, match="one entry per observation"):
+        net.input_custom_sequence((seq, seq), [0, 1], np.ones(5))
+    with pytest.raises(_lib.BackendError, match="single update sequence"):
+        net._launch(values=net._format_series(np.ones(4), None, net.device, False)[0], observed=None, time_steps=None, input_group_size=0,
+                    n_instances=1, params={}, response_fn=0, response_inputs=None, response_group_size=0, response_parameters=None,
+                    record_slots=[], want_last=True, want_sum=False, want_pointwise=False, want_grad=False, group=None, n_groups=0,
+                    branch_idx=[0, 0, 0, 0])

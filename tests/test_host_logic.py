@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(lib):
     L = lib.lib()
     for name in declared:
         assert hasattr(L, name), name
-    assert L.hgf_abi_version() == 3
+    assert L.hgf_abi_version() == 4
     assert lib.launch_count() == 0
 
 
@@ -191,3 +191,21 @@ def test_on_demand_specialisation_builds_and_is_selected(lib):
     assert net.specialise() == name                                      # cached: no rebuild
     L = lib.lib()
     assert L.hgf_register_specialisation(b"/nonexistent.so") != 0 and b"nonexistent" in L.hgf_last_error()
+
+
+def test_switching_plan_lowering(lib):
+    """input_custom_sequence (network.py:653-767): several update sequences in one plan, run by the interpreter."""
+    from pyhgf_b200.network import Network
+    from pyhgf_b200.topology import Plan
+
+    net = nets.binary3(Network).create_belief_propagation_fn()
+    seq = net.update_sequence
+    short = (seq.prediction_steps, tuple(s for s in seq.update_steps if s[0] != 2))
+    args = (net.edges, seq, net.input_idxs, 1, "unbounded", False, 1e10)
+    plan = Plan(*args, branches=(tuple(seq), short))
+    assert plan.n_branches == 2 and plan.kernel_name == "interpreter" and plan.n_slots == net.plan.n_slots
+    assert Plan(*args, branches=(tuple(seq),)).n_branches == 0  # one branch is an ordinary plan
+    with pytest.raises(lib.BackendError, match="branches"):
+        Plan(*args, branches=(tuple(seq),) * 9)
+    with pytest.raises(ValueError, match="update branches"):
+        net.input_custom_sequence((), [0], [1.0])
