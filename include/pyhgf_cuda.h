@@ -203,6 +203,32 @@ typedef struct {
 } hgf_ef_call_t;
 int hgf_ef_filter(const hgf_ef_call_t* call, void* stream);       /* device pointers */
 
+/* Categorical state node (pyhgf/model/add_nodes.py:473-545, pyhgf/utils/fill_categorical_state_node.py:13-81): one binary
+ * HGF per category under the node, run by hgf_filter like any other nodes (the binary nodes are the plan's inputs, one
+ * observation column per category).  This call is the node's own step, categorical_state_update
+ * (pyhgf/updates/posterior/categorical.py:12-91), for every step and instance at once, from the recorded trajectories
+ * of the implied nodes: alpha_t = nu_t * mu_hat_t + 1 with nu_t = (x_t - mu_hat_t) / (sigmoid(mu_parent_t) - mu_hat_t) - 1,
+ * kl_t = KL(Dir(alpha_{t-1}) || Dir(alpha_t)) (pyhgf/math.py:307-341), surprise_t = sum_k binary_surprise(x_tk, mu_hat_tk).
+ * All pointers are device pointers; trajectories are laid out as hgf_filter writes them, [category][T][N]. */
+#define HGF_MAX_CATEGORIES 16
+typedef struct {
+  int32_t dtype;               /* 32 or 64 */
+  int64_t n_instances;         /* N */
+  int32_t n_steps;             /* T */
+  int32_t n_categories;        /* n, 2..HGF_MAX_CATEGORIES */
+  int64_t input_group_size;    /* 0: one observation series for all instances; g > 0: instance i reads series i / g */
+  const void* observations;    /* [G][T][n] the observed category, one-hot */
+  const void* expected_mean;   /* [n][T][N] expected_mean of the binary nodes */
+  const void* parent_mean;     /* [n][T][N] posterior mean of their continuous value parents */
+  const void* alpha0;          /* [n] the concentration before the first step (attributes[node]["alpha"]) */
+  void* alpha;                 /* [n][T][N] or NULL */
+  void* mean;                  /* [n][T][N] or NULL: sigmoid(parent_mean), the node's "mean" after the update */
+  void* kl_divergence;         /* [T][N] */
+  void* surprise;              /* [T][N] */
+} hgf_categorical_call_t;
+
+int hgf_categorical_update(const hgf_categorical_call_t* call, void* stream);
+
 /* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
 int64_t hgf_launch_count(void);
 

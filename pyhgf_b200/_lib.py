@@ -18,6 +18,7 @@ N_FIELDS = 19
 N_RESPONSE_PARAMETERS = 4
 MAX_PARAMS = 16
 MAX_BRANCHES = 8  # HGF_MAX_BRANCHES
+MAX_CATEGORIES = 16  # HGF_MAX_CATEGORIES
 MAX_RECORDS = 640
 
 #: order of the per-node attribute fields inside an instance's attribute vector
@@ -114,7 +115,7 @@ EXPORTS = (
     "hgf_abi_version", "hgf_last_error", "hgf_plan_create", "hgf_plan_destroy", "hgf_plan_n_slots",
     "hgf_plan_slot_coupling", "hgf_plan_slot_clipping", "hgf_plan_slot_response", "hgf_plan_kernel_name",
     "hgf_filter", "hgf_logp_grad", "hgf_filter_host", "hgf_logp_grad_host", "hgf_launch_count",
-    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_register_specialisation", "hgf_ef_filter",
+    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_register_specialisation", "hgf_ef_filter", "hgf_categorical_update",
 )
 
 _lib = None
@@ -135,6 +136,26 @@ class EfCall(C.Structure):
         ("xis0", C.c_void_p),
         ("xis_trajectory", C.c_void_p),
         ("xis_last", C.c_void_p),
+    ]
+
+
+class CategoricalCall(C.Structure):
+    """``hgf_categorical_call_t``"""
+
+    _fields_ = [
+        ("dtype", C.c_int32),
+        ("n_instances", C.c_int64),
+        ("n_steps", C.c_int32),
+        ("n_categories", C.c_int32),
+        ("input_group_size", C.c_int64),
+        ("observations", C.c_void_p),
+        ("expected_mean", C.c_void_p),
+        ("parent_mean", C.c_void_p),
+        ("alpha0", C.c_void_p),
+        ("alpha", C.c_void_p),
+        ("mean", C.c_void_p),
+        ("kl_divergence", C.c_void_p),
+        ("surprise", C.c_void_p),
     ]
 
 
@@ -179,6 +200,8 @@ def lib() -> C.CDLL:
     L.hgf_launch_count.restype = C.c_int64
     L.hgf_ef_filter.argtypes = [C.POINTER(EfCall), C.c_void_p]
     L.hgf_ef_filter.restype = C.c_int
+    L.hgf_categorical_update.argtypes = [C.POINTER(CategoricalCall), C.c_void_p]
+    L.hgf_categorical_update.restype = C.c_int
     L.hgf_register_specialisation.argtypes = [C.c_char_p]
     L.hgf_register_specialisation.restype = C.c_int
     L.hgf_fused_reduce_bytes.argtypes = [C.c_int32, C.c_int32]

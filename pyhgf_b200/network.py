@@ -25,8 +25,8 @@ from typing import Callable, Optional, Sequence, Union
 import numpy as np
 import torch
 
-from . import _lib, ef_state
-from .topology import AdjacencyLists, Plan, get_update_sequence
+from . import _lib, categorical, ef_state
+from .topology import AdjacencyLists, Plan, UpdateSequence, get_update_sequence
 
 _COUPLING_KEYS = ("value_coupling_parents", "volatility_coupling_parents", "value_coupling_children",
                   "volatility_coupling_children")
@@ -69,7 +69,8 @@ def _binary_state_defaults() -> dict:  # add_nodes.py:330-340
 
 _NODE_KINDS = {"continuous-state": (2, _continuous_state_defaults), "volatile-state": (6, _volatile_state_defaults),
                "binary-state": (1, _binary_state_defaults)}
-_OTHER_KINDS = ("dp-state", "categorical-state", "constant-state")
+_OTHER_KINDS = ("dp-state", "constant-state")
+_VECTOR_KINDS = ("ef-state", "categorical-state")  # own kernels beside the scan (ef_state.py, categorical.py)
 
 
 def get_couplings(value_parents, volatility_parents, value_children, volatility_children):
@@ -201,7 +202,7 @@ class Network:
                   value_children=None, value_parents=None, volatility_children=None, volatility_parents=None,
                   coupling_fn: tuple = (None,), **additional_parameters):
         """Add state node(s) (network.py:778-945; defaults add_nodes.py:65-85, 159-184, 330-340)."""
-        if kind not in _NODE_KINDS and kind not in _OTHER_KINDS and kind != "ef-state":
+        if kind not in _NODE_KINDS and kind not in _OTHER_KINDS and kind not in _VECTOR_KINDS:
             raise ValueError(
                 "Invalid node type. Should be one of the following: 'dp-state', 'continuous-state', 'binary-state', "
                 "'ef-state', 'categorical-state', 'volatile-state', or 'constant-state'"
@@ -209,10 +210,12 @@ class Network:
         if kind in _OTHER_KINDS:
             raise NotImplementedError(
                 f"'{kind}' nodes are outside the belief-propagation path this backend accelerates "
-                "(binary-, continuous- and volatile-state nodes, ef-state nodes with a fixed learning rate)"
+                "(binary-, continuous-, volatile- and categorical-state nodes, ef-state nodes with a fixed learning rate)"
             )
         if kind == "ef-state":
             return self._add_ef_state(n_nodes, node_parameters, additional_parameters, value_children)
+        if kind == "categorical-state":
+            return self._add_categorical_state(n_nodes, node_parameters, additional_parameters)
         vp, volp, vc, volc = get_couplings(value_parents, volatility_parents, value_children, volatility_children)
         node_type, make_defaults = _NODE_KINDS[kind]
         if node_type == 6:  # the volatility level is implicit (add_nodes.py:106-202)
@@ -277,6 +280,71 @@ class Network:
             self.n_nodes += 1
         self._invalidate()
         return self
+
+    def _add_categorical_state(self, n_nodes, node_parameters, additional_parameters):
+        """Categorical state node and its implied binary HGFs (add_nodes.py:473-545, fill_categorical_state_node.py:13-81)."""
+        if n_nodes != 1:
+            raise NotImplementedError("add categorical-state nodes one at a time (the reference gives n_nodes > 1 the same binary nodes)")
+        node_parameters = dict(node_parameters or {})
+        n = int(node_parameters.get("n_categories", additional_parameters.get("n_categories", 4)))
+        if not 2 <= n <= _lib.MAX_CATEGORIES:
+            raise ValueError(f"n_categories should be between 2 and {_lib.MAX_CATEGORIES}")
+        params = categorical.defaults(n, 1 + len(self.edges))
+        unknown = [k for k in additional_parameters if k not in params]
+        if unknown:
+            raise ValueError(
+                f"Some parameter(s) passed as keyword arguments were not found in the default key(s) of a categorical-state node "
+                f"(i.e. {list(params.keys())}). If you want to create a new key in the node's attributes, "
+                "please use the node_parameters argument instead."
+            )
+        params.update(additional_parameters)
+        params.update(node_parameters)
+        node = self.n_nodes
+        self.edges = self.edges + (AdjacencyLists(categorical.NODE_TYPE, None, None, None, None, (None,)),)
+        self.attributes[node] = deepcopy(params)
+        self.n_nodes += 1
+        binary = list(params["binary_idxs"])
+        bp = categorical.default_binary_parameters(n)  # as the reference: the DEFAULTS reach the implied network
+        self.add_nodes(kind="binary-state", n_nodes=n, node_parameters={"mean": bp["mean_1"], "precision": bp["precision_1"]})
+        edges = list(self.edges)
+        edges[node] = AdjacencyLists(categorical.NODE_TYPE, tuple(binary), None, None, None, (None,))
+        for b in binary:
+            edges[b] = AdjacencyLists(1, None, None, (node,), None, (None,))
+        self.edges = tuple(edges)
+        for b in binary:
+            self.add_nodes(value_children=b, node_parameters={"mean": bp["mean_2"], "precision": bp["precision_2"],
+                                                              "tonic_volatility": bp["tonic_volatility_2"]})
+        self.add_nodes(volatility_children=[b + n for b in binary],
+                       node_parameters={"mean": bp["mean_3"], "precision": bp["precision_3"], "tonic_volatility": bp["tonic_volatility_3"]})
+        self._invalidate()
+        return self
+
+    def _categorical_nodes(self) -> list:
+        return [i for i, e in enumerate(self.edges) if e.node_type == categorical.NODE_TYPE]
+
+    def _implied_network(self):
+        """(sub-network, {node: sub-network node}): this network without its categorical nodes.  The binary nodes under a
+        categorical input become the inputs, one observation column each (categorical_state_prediction_error,
+        prediction_error/categorical.py:36-45); attributes are copied at call time."""
+        cats = set(self._categorical_nodes())
+        nodes = [i for i in range(self.n_nodes) if i not in cats]
+        local = {g: k for k, g in enumerate(nodes)}
+        sub = Network(volatility_updates=self.volatility_updates, max_posterior_precision=self.max_posterior_precision,
+                      mean_field_updates=self.mean_field_updates, precision_clipping_value=self.attributes[-1]["precision_clipping_value"],
+                      dtype="float32" if self.bits == 32 else "float64", device=self._device)
+        remap = lambda t: None if t is None else (tuple(local[j] for j in t if j not in cats) or None)  # noqa: E731
+        sub.edges = tuple(AdjacencyLists(self.edges[g].node_type, remap(self.edges[g].value_parents), remap(self.edges[g].volatility_parents),
+                                         remap(self.edges[g].value_children), remap(self.edges[g].volatility_children),
+                                         self.edges[g].coupling_fn) for g in nodes)
+        sub.n_nodes = len(nodes)
+        for g in nodes:
+            sub.attributes[local[g]] = deepcopy(self.attributes[g])
+        sub.attributes[-1] = deepcopy(self.attributes[-1])
+        inputs = []
+        for g in self.input_idxs:
+            inputs += [local[b] for b in self.edges[g].value_parents] if g in cats else [local[g]]
+        sub._input_idxs = tuple(inputs)
+        return sub, local
 
     def _ef_nodes(self) -> list:
         """The ef-state nodes, after checking that the network is one this backend runs: the hgf_ef_filter path
@@ -419,6 +487,20 @@ class Network:
         if self._ef_nodes():  # get_input_dimension, network.py:1069-1086; the schedule is one PE step per node
             self.input_dim = [int(self.attributes[i]["dimension"]) for i in self.input_idxs]
             self.update_sequence = ((), tuple((i, "prediction_error_update_exponential_family_fixed") for i in self.input_idxs))
+            self.scan_fn = True
+            return self
+        cats = self._categorical_nodes()
+        if cats:  # the schedule of the implied nodes, framed by the categorical steps (get_update_sequence.py:301-305, 337-345)
+            implied, local = self._implied_network()
+            implied.create_belief_propagation_fn()
+            back = {k: g for g, k in local.items()}
+            seq = implied.update_sequence
+            self.input_dim = [int(self.attributes[i]["n_categories"]) if i in cats else 1 for i in self.input_idxs]
+            self.update_sequence = UpdateSequence(
+                tuple((back[i], f) for i, f in seq.prediction_steps),
+                tuple((c, categorical.categorical_state_prediction_error) for c in cats)
+                + tuple((back[i], f) for i, f in seq.update_steps)
+                + tuple((c, categorical.categorical_state_update) for c in cats))
             self.scan_fn = True
             return self
         self.input_dim = [1 for _ in self.input_idxs]
@@ -681,6 +763,8 @@ class Network:
             self.create_belief_propagation_fn()
         if self._ef_nodes():
             return self._ef_input_data(input_data, time_steps, observed, record_trajectories)
+        if self._categorical_nodes():
+            return self._categorical_input_data(input_data, time_steps, observed)
         self._filter_one_series(input_data, time_steps, observed, record_trajectories)
         self._last_inputs = (input_data, time_steps, observed)
         return self
@@ -699,8 +783,8 @@ class Network:
             self.input_idxs = input_idxs
         if self.scan_fn is None:
             self.create_belief_propagation_fn()
-        if self._ef_nodes():
-            raise NotImplementedError("an ef-state network has a single one-step update sequence")
+        if self._ef_nodes() or self._categorical_nodes():
+            raise NotImplementedError("input_custom_sequence serves binary-, continuous- and volatile-state networks")
         branches = tuple((tuple(b[0]), tuple(b[1])) for b in update_branches)
         if not 1 <= len(branches) <= _lib.MAX_BRANCHES:
             raise ValueError(f"between 1 and {_lib.MAX_BRANCHES} update branches, got {len(branches)}")
@@ -757,6 +841,115 @@ class Network:
             self.node_trajectories = nt
         else:
             self.node_trajectories = None
+
+    # ------------------------------------------------- categorical-state nodes
+    def _categorical_columns(self, n_columns: int) -> list:
+        """[(input node, first column, columns)] over the input nodes (get_input_dimension, network.py:1069-1086)."""
+        out, col = [], 0
+        for i in self.input_idxs:
+            d = int(self.attributes[i]["n_categories"]) if self.edges[i].node_type == categorical.NODE_TYPE else 1
+            out.append((i, col, d))
+            col += d
+        if n_columns != col:
+            raise ValueError(f"input_data has {n_columns} column(s) but the input nodes take {col}")
+        return out
+
+    def _categorical_input_data(self, input_data, time_steps, observed):
+        dev = self.device
+        dt, cast = _torch_dtype(self.bits), _np_dtype(self.bits)
+        x = np.asarray(input_data.cpu() if torch.is_tensor(input_data) else input_data, dtype=np.float64)
+        if x.ndim == 1:
+            x = x[:, None]
+        T = x.shape[0]
+        cols = self._categorical_columns(x.shape[1])
+        masks = None
+        if observed is not None:
+            if isinstance(observed, (tuple, list)):
+                per_node = [np.asarray(o) for o in observed]
+            else:
+                o = np.asarray(observed)
+                per_node = [o] if o.ndim == 1 else [o[:, k] for k in range(o.shape[1])]
+            masks = {i: per_node[j] for j, (i, _, _) in enumerate(cols)}
+        implied, local = self._implied_network()
+        expanded = None if masks is None else np.stack([masks[i] for i, _, d in cols for _ in range(d)], axis=1)
+        implied.input_data(x, time_steps=time_steps, observed=expanded, record_trajectories=True)
+        back = {k: g for g, k in local.items()}
+        nt = {back[k]: v for k, v in implied.node_trajectories.items() if k != -1}
+        nt[-1] = implied.node_trajectories[-1]
+        last = deepcopy(self.attributes)
+        for k, g in back.items():
+            last[g] = implied.last_attributes[k]
+        last[-1] = implied.last_attributes[-1]
+        for c, c0, n in cols:
+            if self.edges[c].node_type != categorical.NODE_TYPE:
+                continue
+            binary = self.edges[c].value_parents
+            em = np.stack([nt[b]["expected_mean"] for b in binary])  # [n][T]
+            pm = np.stack([nt[self.edges[b].value_parents[0]]["mean"] for b in binary])
+            out = categorical.update(bits=self.bits, device=dev,
+                                     observations=torch.as_tensor(np.ascontiguousarray(x[None, :, c0:c0 + n])).to(device=dev, dtype=dt),
+                                     expected_mean=torch.as_tensor(em).to(device=dev, dtype=dt)[:, :, None].contiguous(),
+                                     parent_mean=torch.as_tensor(pm).to(device=dev, dtype=dt)[:, :, None].contiguous(),
+                                     alpha0=self.attributes[c]["alpha"], input_group_size=0)
+            seen = np.ones(T, dtype=np.int64) if masks is None else (masks[c] != 0).astype(np.int64)
+            nt[c] = {"n_categories": np.full(T, n), "binary_idxs": np.broadcast_to(np.asarray(binary), (T, n)),
+                     "alpha": out["alpha"][:, :, 0].t().cpu().numpy(), "mean": out["mean"][:, :, 0].t().cpu().numpy(),
+                     "kl_divergence": out["kl_divergence"][:, 0].cpu().numpy(), "surprise": out["surprise"][:, 0].cpu().numpy(),
+                     "observed": seen}
+            if T:
+                for key in ("alpha", "mean", "kl_divergence", "surprise", "observed"):
+                    last[c][key] = nt[c][key][-1]
+        self.node_trajectories = nt
+        self.last_attributes = last
+        self._last_inputs = (input_data, time_steps, observed)
+        return self
+
+    def _categorical_batch(self, input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream):
+        """``batch`` with categorical nodes: the implied network's batch, then one hgf_categorical_update per node whose
+        ``(node, "kl_divergence" | "surprise" | "alpha" | "mean")`` is recorded."""
+        implied, local = self._implied_network()
+        cats = self._categorical_nodes()
+        own = [tuple(k) for k in record if k[0] in cats]
+        if any(k[1] not in ("kl_divergence", "surprise", "alpha", "mean") for k in own):
+            raise ValueError("a categorical node records 'kl_divergence', 'surprise', 'alpha' or 'mean'")
+        params = {}
+        for k, v in parameters.items():
+            if isinstance(k, (tuple, list)) and isinstance(k[0], (int, np.integer)) and k[0] >= 0:
+                if k[0] in cats:
+                    raise ValueError("the parameters of a categorical node's binary HGFs live on the implied nodes")
+                params[(local[k[0]],) + tuple(k[1:])] = v
+            else:
+                params[k] = v
+        rec = [(local[k[0]],) + tuple(k[1:]) for k in record if k[0] not in cats]
+        needed = {}
+        for c in sorted({k[0] for k in own}):
+            binary = self.edges[c].value_parents
+            needed[c] = ([(local[b], "expected_mean") for b in binary], [(local[self.edges[b].value_parents[0]], "mean") for b in binary])
+        extra = [k for pair in needed.values() for group in pair for k in group if k not in rec]
+        if observed is not None:
+            raise NotImplementedError("observation masks with categorical nodes go through input_data")
+        res = implied.batch(input_data, params, time_steps=time_steps, n_instances=n_instances, input_group_size=input_group_size,
+                            record=rec + list(dict.fromkeys(extra)), stream=stream)
+        traj = res.trajectories
+        dev, dt = self.device, _torch_dtype(self.bits)
+        x = torch.as_tensor(np.asarray(input_data) if not torch.is_tensor(input_data) else input_data).to(device=dev, dtype=dt)
+        x = x[None] if input_group_size <= 0 else x
+        cols = {i: (c0, d) for i, c0, d in self._categorical_columns(x.shape[2])}
+        back = {k: g for g, k in local.items()}
+        out = {(back[k[0]],) + tuple(k[1:]): v for k, v in traj.items() if k in rec}
+        for c, (em_keys, pm_keys) in needed.items():
+            c0, n = cols[c]
+            em = torch.stack([traj[k].t() for k in em_keys]).contiguous()  # [n][T][N]
+            pm = torch.stack([traj[k].t() for k in pm_keys]).contiguous()
+            want_vec = any(k[0] == c and k[1] in ("alpha", "mean") for k in own)
+            r = categorical.update(bits=self.bits, device=dev, observations=x[:, :, c0:c0 + n].contiguous(), expected_mean=em,
+                                   parent_mean=pm, alpha0=self.attributes[c]["alpha"], input_group_size=input_group_size,
+                                   want_vectors=want_vec)
+            for k in own:
+                if k[0] == c:
+                    out[k] = r[k[1]].t() if k[1] in ("kl_divergence", "surprise") else r[k[1]].permute(2, 1, 0)
+        res.trajectories = out
+        return res
 
     # ---------------------------------------------------- ef-state networks
     def _ef_columns(self, n_columns: int) -> list:
@@ -1072,6 +1265,10 @@ class Network:
             if response_function is not None or gradient or pointwise or fused_reduce is not None or time_steps is not None:
                 raise NotImplementedError("an ef-state network has no response function, gradient or time steps on this path")
             return self._ef_batch(input_data, parameters, observed, n_instances, input_group_size, record, last_attributes)
+        if self._categorical_nodes():
+            if response_function is not None or gradient or pointwise or fused_reduce is not None or last_attributes:
+                raise NotImplementedError("a network with categorical nodes batches trajectories (record=[...]) on this path")
+            return self._categorical_batch(input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream)
         dev = self.device
         split = self._split_over_components(input_data, parameters, response_function, response_function_inputs,
                                             response_function_parameters, time_steps, observed, n_instances, input_group_size,

@@ -1023,3 +1023,64 @@ def test_custom_sequence_abi_errors(G):
                     n_instances=1, params={}, response_fn=0, response_inputs=None, response_group_size=0, response_parameters=None,
                     record_slots=[], want_last=True, want_sum=False, want_pointwise=False, want_grad=False, group=None, n_groups=0,
                     branch_idx=[0, 0, 0, 0])
+
+
+# ---------------------------------------------------------------- categorical-state nodes (hgf_categorical_update)
+def test_categorical_reference_golden(G):
+    """tests/test_categorical.py:9-88 through the drop-in surface: same calls, same goldens."""
+    np.random.seed(123)
+    x = np.array([np.random.multinomial(n=1, pvals=[0.1, 0.2, 0.7]) for _ in range(10)], dtype=float)
+    net = G.Network().add_nodes(kind="categorical-state", node_parameters={"n_categories": 3, "binary_parameters": {"tonic_volatility_2": -2.0}})
+    net.input_data(input_data=x)
+    net.to_pandas()
+    assert np.isclose(net.node_trajectories[0]["kl_divergence"].sum(), 1.2642910)
+    assert np.isclose(net.node_trajectories[0]["surprise"].sum(), 12.418026)
+    assert net.node_trajectories[0]["alpha"].shape == (10, 3) and net.node_trajectories[4]["mean"].shape == (10,)
+    assert np.array_equal(net.node_trajectories[2]["mean"], x[:, 1].astype(np.float32))
+    assert np.isclose(net.last_attributes[0]["kl_divergence"], net.node_trajectories[0]["kl_divergence"][-1])
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("n", [2, 3, 5, 9])
+def test_categorical_matches_oracle(G, n, dtype):
+    from oracle import categorical as cat
+
+    rng = np.random.default_rng(100 + n)
+    p = rng.dirichlet(np.ones(n))
+    x = rng.multinomial(1, p, size=60).astype(float)
+    net = G.Network(dtype=dtype).add_nodes(kind="categorical-state", node_parameters={"n_categories": n}).input_data(x)
+    onet_, c = cat.categorical_filter(x, n, None, dtype=dtype)
+    rt = RTOL_TRAJ if dtype == "float32" else 1e-9
+    for k in range(n):  # the implied binary HGFs: binary k is node 1 + k here, node k in the oracle's implied network
+        for key in ("expected_mean", "mean"):
+            assert np.allclose(net.node_trajectories[1 + n + k][key], onet_.node_trajectories[n + k][key], rtol=rt, atol=1e-7)
+        assert np.allclose(net.node_trajectories[1 + k]["expected_mean"], onet_.node_trajectories[k]["expected_mean"], rtol=rt, atol=1e-7)
+    got = net.node_trajectories[0]
+    # nu divides by (sigmoid(mu) - mu_hat), a difference of nearby numbers: alpha carries the amplified rounding of both runs
+    amp = 1e-3 if dtype == "float32" else 1e-7
+    assert np.allclose(got["alpha"], c["alpha"], rtol=amp), np.abs(got["alpha"] / c["alpha"] - 1).max()
+    assert np.allclose(got["mean"], c["mean"], rtol=rt)
+    assert np.allclose(got["surprise"], c["surprise"], rtol=RTOL_SUM if dtype == "float32" else 1e-9)
+    assert np.allclose(got["kl_divergence"], c["kl_divergence"], rtol=10 * amp, atol=amp)
+    assert np.isclose(got["kl_divergence"].sum(), c["kl_divergence"].sum(), rtol=10 * amp)
+
+
+def test_categorical_batch(G):
+    """Instances that differ in the tonic volatility of the implied continuous nodes; per-instance result = single runs."""
+    rng = np.random.default_rng(8)
+    n, N, T = 4, 96, 50
+    x = rng.multinomial(1, [0.1, 0.2, 0.3, 0.4], size=T).astype(float)
+    om = rng.uniform(-5.0, -2.0, N)
+    net = G.Network().add_nodes(kind="categorical-state", node_parameters={"n_categories": n})
+    params = {(1 + n + k, "tonic_volatility"): om for k in range(n)}
+    r = net.batch(x, params, record=[(0, "kl_divergence"), (0, "surprise"), (0, "alpha"), (1 + n, "mean")])
+    kl, s, alpha = (r.trajectories[(0, k)].cpu().numpy() for k in ("kl_divergence", "surprise", "alpha"))
+    assert kl.shape == (N, T) and alpha.shape == (N, T, n) and r.trajectories[(1 + n, "mean")].shape == (N, T)
+    for i in (0, 17, 95):
+        one = G.Network().add_nodes(kind="categorical-state", node_parameters={"n_categories": n})
+        for k in range(n):
+            one.attributes[1 + n + k]["tonic_volatility"] = float(om[i])
+        one.input_data(x)
+        assert np.allclose(kl[i], one.node_trajectories[0]["kl_divergence"], rtol=1e-4, atol=1e-6)
+        assert np.allclose(s[i], one.node_trajectories[0]["surprise"], rtol=1e-5)
+        assert np.allclose(alpha[i], one.node_trajectories[0]["alpha"], rtol=1e-4)

@@ -47,6 +47,7 @@ def test_struct_layouts_match_the_header(lib):
     assert fields("hgf_topology_t") == [f[0] for f in lib.Topology._fields_]
     assert fields("hgf_call_t") == [f[0] for f in lib.Call._fields_]
     assert fields("hgf_ef_call_t") == [f[0] for f in lib.EfCall._fields_]
+    assert fields("hgf_categorical_call_t") == [f[0] for f in lib.CategoricalCall._fields_]
 
 
 def test_ef_state_node_defaults(lib):
@@ -124,7 +125,7 @@ def test_api_errors_match_the_reference(lib):
     with pytest.raises(ValueError, match="coupling fn and value children do not match"):
         Network().add_nodes(n_nodes=3).add_nodes(value_children=[0, 1, 2], coupling_fn=(None, None))
     with pytest.raises(NotImplementedError):
-        Network().add_nodes(kind="categorical-state")
+        Network().add_nodes(kind="dp-state")
     net = Network().add_nodes().add_nodes(value_children=0)
     assert net.input_idxs == (0,)
     assert net.attributes[0]["autoconnection_strength"] == 0.0 and net.attributes[0]["tonic_volatility"] == 0.0
@@ -209,3 +210,36 @@ def test_switching_plan_lowering(lib):
         Plan(*args, branches=(tuple(seq),) * 9)
     with pytest.raises(ValueError, match="update branches"):
         net.input_custom_sequence((), [0], [1.0])
+
+
+def test_categorical_state_structure(lib):
+    """tests/test_categorical.py:19-72: the implied network of a categorical node and its coupling bookkeeping."""
+    from pyhgf_b200.network import Network
+
+    net = Network().add_nodes(kind="categorical-state", node_parameters={"n_categories": 3, "binary_parameters": {"tonic_volatility_2": -2.0}})
+    assert [e.node_type for e in net.edges] == [5, 1, 1, 1, 2, 2, 2, 2]
+    assert net.edges[0].value_parents == (1, 2, 3) and net.edges[2].value_children == (0,) and net.edges[2].value_parents == (5,)
+    assert net.edges[7].volatility_children == (4, 5, 6) and net.edges[5].volatility_parents == (7,)
+    for i, e in enumerate(net.edges):
+        if e.node_type == 2:
+            for field, key in (("value_parents", "value_coupling_parents"), ("value_children", "value_coupling_children"),
+                               ("volatility_parents", "volatility_coupling_parents"), ("volatility_children", "volatility_coupling_children")):
+                if getattr(e, field):
+                    assert len(getattr(e, field)) == len(net.attributes[i][key])
+                else:
+                    assert getattr(e, field) is None and net.attributes[i][key] is None
+    a = net.attributes[0]
+    assert a["binary_idxs"] == [1, 2, 3] and np.array_equal(a["alpha"], np.ones(3)) and np.allclose(a["mean"], 1 / 3)
+    # the reference hands the DEFAULT binary parameters to the implied network (add_nodes.py:532-537)
+    assert net.attributes[4]["tonic_volatility"] == -4.0 and a["binary_parameters"] == {"tonic_volatility_2": -2.0}
+    assert np.isclose(net.attributes[4]["mean"], -np.log(2.0)) and net.attributes[1]["mean"] == 1 / 3
+    net.create_belief_propagation_fn()
+    assert net.input_idxs == (0,) and net.input_dim == [3]
+    steps = [(i, f.__name__) for i, f in net.update_sequence.update_steps]
+    assert steps[0] == (0, "categorical_state_prediction_error") and steps[-1] == (0, "categorical_state_update")
+    assert (7, "continuous_node_posterior_update_unbounded") in steps
+    implied, local = net._implied_network()
+    assert implied.input_idxs == (0, 1, 2) and [e.node_type for e in implied.edges] == [1, 1, 1, 2, 2, 2, 2]
+    assert implied.edges[0].value_children is None
+    with pytest.raises(ValueError, match="n_categories"):
+        Network().add_nodes(kind="categorical-state", node_parameters={"n_categories": 40})

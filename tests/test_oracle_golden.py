@@ -475,3 +475,19 @@ def test_exponential_family_fixed_learning_rate_golden():
     mask = (np.arange(len(x)) % 3 != 0)
     held = ef.ef_filter(x, 3.0, 2, "multivariate-normal", observed=mask)
     assert np.array_equal(held[3], held[2]) and not np.array_equal(held[4], held[3])
+
+
+def test_categorical_state_node_golden():
+    """tests/test_categorical.py:9-88: summed KL divergence and surprise of the 3-category example.  The reference builds
+    the implied binary HGFs from its default parameters whatever ``binary_parameters`` says (add_nodes.py:532-537)."""
+    from oracle import categorical as cat
+
+    np.random.seed(123)
+    x = np.array([np.random.multinomial(n=1, pvals=[0.1, 0.2, 0.7]) for _ in range(10)], dtype=float)
+    _, c = cat.categorical_filter(x, 3, None, dtype="float32")
+    assert np.isclose(c["kl_divergence"].sum(), 1.2642910) and np.isclose(c["surprise"].sum(), 12.418026)
+    _, c64 = cat.categorical_filter(x, 3, None, dtype="float64")
+    assert np.isclose(c64["kl_divergence"].sum(), 1.2642910) and np.isclose(c64["surprise"].sum(), 12.418026)
+    assert np.allclose(c["alpha"], c64["alpha"], rtol=1e-4) and (c64["alpha"] > 0).all()
+    _, other = cat.categorical_filter(x, 3, {"tonic_volatility_2": -2.0}, dtype="float32")
+    assert not np.isclose(other["surprise"].sum(), 12.418026)  # the override would change the answer
