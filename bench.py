@@ -206,6 +206,7 @@ def e2e_leg(net, plan, u, y, params, steps, warmup, device_index):
     call.response_fn = _lib.RESPONSES["binary_softmax_inverse_temperature"]
     call.surprise_sum, call.gradient, call.reduced, call.group = h_logp.data_ptr(), h_grad.data_ptr(), h_red.data_ptr(), h_group.data_ptr()
     call.out_scale = -1.0
+    call.n_groups = N_CHAINS
     h2d = sum(t.numel() * t.element_size() for t in (h_u, h_y, h_p, h_attr, h_group, h_red))
     d2h = sum(t.numel() * t.element_size() for t in (h_logp, h_grad, h_red))
     for _ in range(warmup):

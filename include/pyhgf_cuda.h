@@ -126,7 +126,7 @@ typedef struct {
    * workspace + hgf_fused_reduce_result_offset(n_groups, dtype, epoch) holds the all-reduced [G] sums; they stay
    * valid until the launch after next.  `reduced` must be NULL; `epoch` counts the launches on this workspace
    * (0, 1, 2, ...) and must be the same on every rank. */
-  int32_t n_groups;              /* G */
+  int32_t n_groups;              /* G (also read by the *_host entry points: > 0 saves their scan of group[] for its maximum) */
   int32_t world_size;            /* W <= 8 */
   int32_t rank;
   uint32_t epoch;

@@ -362,7 +362,8 @@ namespace {
 // Per-thread, per-device staging context of the *_host entry points: one non-blocking stream and one device
 // arena that only grows, so that a sampler calling hgf_logp_grad_host thousands of times pays for stream
 // creation and device allocation once (they cost more than the copies themselves for a 65 536-instance batch).
-constexpr int kHostChunks = 4;
+constexpr int kHostChunks = 8;         // most slices of the chunk pipeline (streams are created once)
+constexpr int kDefaultHostChunks = 4;  // HGF_HOST_CHUNKS=n overrides (0 / 1: one-shot path)
 struct HostContext {
   int device = -1;
   cudaStream_t stream = nullptr;
@@ -450,7 +451,10 @@ struct Staging {
 // a pointer offset.  Returns -1 when the call is not eligible (then the one-shot path below runs), else the result.
 static int run_host_chunked(const hgf_plan_t* plan, const hgf_call_t* c, bool want_grad, int n_groups) {
   const char* env = std::getenv("HGF_HOST_CHUNKS");
-  if (env && env[0] == '0') return -1;
+  int n_chunks = kDefaultHostChunks;
+  if (env && env[0] >= '0' && env[0] <= '9') n_chunks = env[0] - '0';
+  if (n_chunks < 2) return -1;
+  if (n_chunks > kHostChunks) n_chunks = kHostChunks;
   const Program& p = plan->prog;
   const long long N = c->n_instances;
   if (N < 32768 || c->trajectories || c->surprise_pointwise || c->last_attributes || c->world_size > 1 || c->generative || c->branch_idx) return -1;
@@ -459,7 +463,7 @@ static int run_host_chunked(const hgf_plan_t* plan, const hgf_call_t* c, bool wa
   long long unit = 64;
   if (c->input_group_size > 0) unit = lcm(unit, c->input_group_size);
   if (c->response_group_size > 0) unit = lcm(unit, c->response_group_size);
-  const long long per = ((N + kHostChunks - 1) / kHostChunks + unit - 1) / unit * unit;
+  const long long per = ((N + n_chunks - 1) / n_chunks + unit - 1) / unit * unit;
   if (per <= 0 || per >= N) return -1;
   const size_t w = c->dtype == 32 ? 4 : 8, T = static_cast<size_t>(c->n_steps), F = static_cast<size_t>(p.n_fed), P = static_cast<size_t>(c->n_params);
   const size_t in_series = c->input_group_size > 0 ? (N + c->input_group_size - 1) / c->input_group_size : 1;
@@ -550,8 +554,11 @@ static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, boo
   const size_t n_in_series = c->input_group_size > 0 ? (N + c->input_group_size - 1) / c->input_group_size : 1;
   const size_t n_resp_series = c->response_group_size > 0 ? (N + c->response_group_size - 1) / c->response_group_size : 1;
   int n_groups = 1;
-  if (c->reduced && c->group)
-    for (size_t i = 0; i < N; ++i) n_groups = c->group[i] + 1 > n_groups ? c->group[i] + 1 : n_groups;
+  if (c->reduced && c->group) {
+    if (c->n_groups > 0) n_groups = c->n_groups;  // the caller's count saves a pass over group[]
+    else
+      for (size_t i = 0; i < N; ++i) n_groups = c->group[i] + 1 > n_groups ? c->group[i] + 1 : n_groups;
+  }
   // (pointer, bytes) of every staged array, in the order they are taken below
   const size_t sz_in = n_in_series * T * p.n_fed * w, sz_obs = n_in_series * T * p.n_fed, sz_ts = T * w;
   const size_t sz_attr = static_cast<size_t>(p.n_slots) * w, sz_par = static_cast<size_t>(c->n_params) * N * w;

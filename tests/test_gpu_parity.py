@@ -740,8 +740,8 @@ def test_generative_rollouts(G, datasets):
 
 @pytest.mark.parametrize("n_part,n_chain,shared", [(800, 50, False), (1, 40000, True), (1024, 64, False)])
 def test_host_entry_point_chunk_pipeline(G, n_part, n_chain, shared, monkeypatch):
-    """hgf_logp_grad_host on a large batch: the chunked copy/compute pipeline (4 slices of whole series groups on 4
-    streams, ScanArgs::ld row strides) returns exactly what the one-shot path (HGF_HOST_CHUNKS=0) returns, for grouped
+    """hgf_logp_grad_host on a large batch: the chunked copy/compute pipeline (HGF_HOST_CHUNKS slices of whole series groups, one stream
+    each, ScanArgs::ld row strides) returns exactly what the one-shot path (HGF_HOST_CHUNKS=0) returns, for grouped
     series whose group size does not divide the block size, and for one shared series."""
     from pyhgf_b200 import _lib
 
@@ -758,7 +758,7 @@ def test_host_entry_point_chunk_pipeline(G, n_part, n_chain, shared, monkeypatch
     attr = net._flatten(plan)
     slots = (C.c_int32 * 3)(plan.slot(1, "tonic_volatility"), plan.slot(2, "tonic_volatility"), plan.slot(-1, "response_parameter", 0))
     out = {}
-    for flag in ("1", "0"):
+    for flag in ("4", "0", "3"):
         monkeypatch.setenv("HGF_HOST_CHUNKS", flag)
         logp, grad, red = np.zeros(n, np.float32), np.zeros((3, n), np.float32), np.zeros(7, np.float32)
         call = _lib.Call()
@@ -772,10 +772,11 @@ def test_host_entry_point_chunk_pipeline(G, n_part, n_chain, shared, monkeypatch
         before = _lib.launch_count()
         _lib.check(_lib.lib().hgf_logp_grad_host(plan.handle, C.byref(call), 0))
         out[flag] = (logp, grad, red, _lib.launch_count() - before)
-    assert out["1"][3] == 4 and out["0"][3] == 1                     # four slices vs one launch
-    assert np.array_equal(out["1"][0], out["0"][0]) and np.array_equal(out["1"][1], out["0"][1])
-    assert np.isfinite(out["1"][0]).all()
-    assert np.allclose(out["1"][2], out["0"][2], rtol=1e-5)          # atomics: order differs
+    assert out["4"][3] == 4 and out["0"][3] == 1 and out["3"][3] == 3  # slices = launches; 0 is the one-shot path
+    for flag in ("4", "3"):
+        assert np.array_equal(out[flag][0], out["0"][0]) and np.array_equal(out[flag][1], out["0"][1])
+        assert np.allclose(out[flag][2], out["0"][2], rtol=1e-5)       # atomics: order differs
+    assert np.isfinite(out["4"][0]).all()
 
 
 def test_committed_golden_vectors(G, R, datasets):
