@@ -200,6 +200,13 @@ typedef struct {
   const void* xis0;            /* [K] initial sufficient statistics, shared */
   void* xis_trajectory;        /* [K][T][N] or NULL */
   void* xis_last;              /* [K][N] or NULL */
+  /* learning = "hgf-1|2|3" (add_nodes.py:438-452, posterior_update_exponential_family_dynamic,
+   * pyhgf/updates/posterior/exponential.py): the learning rate of step t is implied by the continuous HGFs that track the
+   * sufficient statistics, nu_t = mean_k (A_k.mean - A_k.expected_mean) / (B_k.mean - B_k.expected_mean), A_k the node
+   * fed with statistic k and B_k its value parent.  implied = their trajectories as hgf_filter records them,
+   * [4][K][T][N] in the order A.mean, A.expected_mean, B.mean, B.expected_mean; nus is then ignored. */
+  const void* implied;         /* NULL: fixed learning rate (nus) */
+  void* nus_trajectory;        /* [T][N] or NULL: the implied nu_t */
 } hgf_ef_call_t;
 int hgf_ef_filter(const hgf_ef_call_t* call, void* stream);       /* device pointers */
 

@@ -136,6 +136,8 @@ class EfCall(C.Structure):
         ("xis0", C.c_void_p),
         ("xis_trajectory", C.c_void_p),
         ("xis_last", C.c_void_p),
+        ("implied", C.c_void_p),
+        ("nus_trajectory", C.c_void_p),
     ]
 
 

@@ -22,7 +22,8 @@ __global__ void __launch_bounds__(128) ef_fixed_kernel(hgf_ef_call_t c) {
   const B* x = static_cast<const B*>(c.input_data) + series * T * D;
   const uint8_t* obs = c.observed ? c.observed + series * T : nullptr;
   // exponential.py:50-52: xis + (1 / (1 + nus)) * (observation_ss - xis)
-  const B w = b_div(B(1), B(1) + HGF_LDG(static_cast<const B*>(c.nus) + n));
+  const B* implied = static_cast<const B*>(c.implied);
+  B w = implied ? B(0) : b_div(B(1), B(1) + HGF_LDG(static_cast<const B*>(c.nus) + n));
   B xis[K];
 #pragma unroll
   for (int k = 0; k < K; ++k) xis[k] = HGF_LDG(static_cast<const B*>(c.xis0) + k);
@@ -39,6 +40,18 @@ __global__ void __launch_bounds__(128) ef_fixed_kernel(hgf_ef_call_t c) {
 #pragma unroll
       for (int q = 0; q <= r; ++q) ss[k++] = v[r] * v[q];
     const bool seen = obs ? HGF_LDG(obs + t) != 0 : true;
+    if (implied) {  // posterior/exponential.py: pe / expectation differential, averaged over the statistics
+      const long long plane = static_cast<long long>(K) * T * N, at = static_cast<long long>(t) * N + n;
+      B nu = B(0);
+#pragma unroll
+      for (int j = 0; j < K; ++j) {
+        const long long o = static_cast<long long>(j) * T * N + at;
+        nu += b_div(HGF_LDG(implied + o) - HGF_LDG(implied + plane + o), HGF_LDG(implied + 2 * plane + o) - HGF_LDG(implied + 3 * plane + o));
+      }
+      nu = nu / B(K);
+      w = b_div(B(1), B(1) + nu);
+      if (c.nus_trajectory) static_cast<B*>(c.nus_trajectory)[at] = nu;
+    }
 #pragma unroll
     for (int j = 0; j < K; ++j) {
       const B next = xis[j] + w * (ss[j] - xis[j]);
@@ -73,7 +86,7 @@ extern "C" int hgf_ef_filter(const hgf_ef_call_t* c, void* stream) {
   if (c->dimension < 1 || c->dimension > 8) return report_error("hgf_ef_filter: dimension outside [1, 8]");
   if (c->n_instances < 0 || c->n_steps < 0 || c->input_group_size < 0) return report_error("hgf_ef_filter: negative size");
   if (c->n_instances == 0) return 0;
-  if (!c->nus || !c->xis0 || (c->n_steps > 0 && !c->input_data)) return report_error("hgf_ef_filter: null input");
+  if ((!c->nus && !c->implied) || !c->xis0 || (c->n_steps > 0 && !c->input_data)) return report_error("hgf_ef_filter: null input");
   const cudaError_t e = c->dtype == 32 ? launch_ef<float>(*c, static_cast<cudaStream_t>(stream)) : launch_ef<double>(*c, static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) {
     char buf[256];

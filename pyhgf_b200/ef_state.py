@@ -6,8 +6,9 @@ Mirrors ``add_ef_state`` (pyhgf/model/add_nodes.py:360-470) and the update the s
 parents, so every node is its own time loop over its ``dimension`` input columns; one launch filters a batch
 of instances that differ in ``nus`` (and optionally in their series).
 
-Only ``learning="generalised-filtering"`` is served: the ``hgf-*`` variants build continuous-state
-sub-networks under the node and are left to a later round.
+``learning="hgf-1|2|3"`` (add_nodes.py:438-452) puts continuous HGFs under the node, one per sufficient statistic; they
+run on the ordinary scan as its inputs, fed with t(x) (``Network._implied_network``), and ``hgf_ef_filter`` takes their
+trajectories to form the per-step learning rate (``implied``).
 """
 
 from __future__ import annotations
@@ -21,6 +22,17 @@ from . import _lib
 
 NODE_TYPE = 3
 MAX_DIMENSION = 8  # template instances of ef_fixed_kernel (csrc/hgf_ef.cu)
+
+
+def prediction_error_update_exponential_family_dynamic(*args, **kwargs):
+    """Schedule marker (pyhgf/updates/prediction_error/exponential.py:63-120): t(x) goes to the continuous nodes that
+    track the statistics -- here they are the scan's inputs, fed with t(x)."""
+    raise RuntimeError("schedule marker: the step runs inside the CUDA time loop")
+
+
+def posterior_update_exponential_family_dynamic(*args, **kwargs):
+    """Schedule marker (pyhgf/updates/posterior/exponential.py): runs inside hgf_ef_filter (per-step learning rate)."""
+    raise RuntimeError("schedule marker: the step runs as hgf_ef_filter")
 
 
 def n_sufficient_statistics(d: int) -> int:
@@ -38,11 +50,8 @@ def finish_parameters(params: dict) -> dict:
     dist = params["distribution"]
     if dist not in ("normal", "multivariate-normal"):
         raise ValueError("The distribution should be either 'normal' or 'multivariate-normal'.")
-    if "hgf" in str(params["learning"]):
-        raise NotImplementedError(
-            "ef-state nodes are accelerated for learning='generalised-filtering' (fixed learning rate); "
-            f"'{params['learning']}' builds continuous-state sub-networks under the node, which this backend does not lower yet"
-        )
+    if str(params["learning"]) not in ("generalised-filtering", "hgf-1", "hgf-2", "hgf-3"):
+        raise ValueError("learning should be 'generalised-filtering', 'hgf-1', 'hgf-2' or 'hgf-3'")
     if dist == "normal" and d != 1:
         raise ValueError("a 'normal' ef-state node has dimension 1; use 'multivariate-normal'")
     if not 1 <= d <= MAX_DIMENSION:
@@ -65,13 +74,14 @@ def sufficient_statistics(x: np.ndarray, d: int) -> np.ndarray:
     return np.concatenate([x, x[:, r] * x[:, q]], axis=1)
 
 
-def launch(*, bits: int, device, series: torch.Tensor, observed, nus: torch.Tensor, xis0: np.ndarray, dimension: int,
-           input_group_size: int, want_trajectory: bool):
-    """One ``hgf_ef_filter`` launch. series [G][T][d], nus [N] (device tensors) -> (trajectory [K][T][N] | None, last [K][N])."""
+def launch(*, bits: int, device, series: torch.Tensor, observed, nus, xis0: np.ndarray, dimension: int,
+           input_group_size: int, want_trajectory: bool, implied=None):
+    """One ``hgf_ef_filter`` launch. series [G][T][d], nus [N] (device tensors) -> (trajectory [K][T][N] | None, last [K][N]).
+    With ``implied`` [4][K][T][N] (learning="hgf-*") the learning rate is per step and a third result, nus [T][N], is returned."""
     L = _lib.lib()
     tdt = torch.float32 if bits == 32 else torch.float64
     G, T, d = series.shape
-    N = int(nus.shape[0])
+    N = int(nus.shape[0]) if implied is None else int(implied.shape[3])
     K = n_sufficient_statistics(dimension)
     if d != dimension or len(xis0) != K:
         raise ValueError("series / xis do not match the node's dimension")
@@ -86,10 +96,16 @@ def launch(*, bits: int, device, series: torch.Tensor, observed, nus: torch.Tens
     c.input_group_size = int(input_group_size)
     c.input_data = series.data_ptr()
     c.observed = observed.data_ptr() if observed is not None else None
-    c.nus = nus.data_ptr()
+    c.nus = nus.data_ptr() if implied is None else None
+    nus_t = None
+    if implied is not None:
+        if tuple(implied.shape) != (4, K, T, N) or not implied.is_contiguous():
+            raise ValueError("implied should be a contiguous [4][K][T][N] tensor")
+        nus_t = torch.empty((T, N), dtype=tdt, device=device)
+        c.implied, c.nus_trajectory = implied.data_ptr(), nus_t.data_ptr()
     c.xis0 = x0.data_ptr()
     c.xis_trajectory = traj.data_ptr() if traj is not None else None
     c.xis_last = last.data_ptr()
     s = torch.cuda.current_stream(device)  # the temporaries above are freed in this stream's order
     _lib.check(L.hgf_ef_filter(C.byref(c), C.c_void_p(s.cuda_stream)))
-    return traj, last
+    return (traj, last) if implied is None else (traj, last, nus_t)

@@ -273,11 +273,23 @@ class Network:
             )
         params.update(additional_parameters)
         params.update(node_parameters or {})
+        learning = str(params["learning"])
         params = ef_state.finish_parameters(params)
+        if "hgf" in learning and n_nodes != 1:
+            raise NotImplementedError("add ef-state nodes with learning='hgf-*' one at a time")
         for _ in range(n_nodes):
+            node = self.n_nodes
             self.edges = self.edges + (AdjacencyLists(ef_state.NODE_TYPE, None, None, None, None, (None,)),)
-            self.attributes[self.n_nodes] = deepcopy(params)
+            self.attributes[node] = deepcopy(params)
             self.n_nodes += 1
+            if "hgf" in learning:  # continuous nodes tracking each sufficient statistic (add_nodes.py:438-452)
+                for _k in range(ef_state.n_sufficient_statistics(int(params["dimension"]))):
+                    self.add_nodes(value_children=node)
+                    self.add_nodes(value_children=self.n_nodes - 1)
+                    if "-2" in learning or "-3" in learning:
+                        self.add_nodes(volatility_children=self.n_nodes - 1)
+                    if "-3" in learning:
+                        self.add_nodes(volatility_children=self.n_nodes - 1)
         self._invalidate()
         return self
 
@@ -322,11 +334,18 @@ class Network:
     def _categorical_nodes(self) -> list:
         return [i for i, e in enumerate(self.edges) if e.node_type == categorical.NODE_TYPE]
 
+    def _vector_nodes(self) -> list:
+        """Nodes whose own step runs beside the scan, on the trajectories of the nodes implied under them: categorical
+        nodes and ef-state nodes with learning='hgf-*' (those have value parents)."""
+        return [i for i, e in enumerate(self.edges)
+                if e.node_type == categorical.NODE_TYPE or (e.node_type == ef_state.NODE_TYPE and e.value_parents is not None)]
+
     def _implied_network(self):
-        """(sub-network, {node: sub-network node}): this network without its categorical nodes.  The binary nodes under a
-        categorical input become the inputs, one observation column each (categorical_state_prediction_error,
-        prediction_error/categorical.py:36-45); attributes are copied at call time."""
-        cats = set(self._categorical_nodes())
+        """(sub-network, {node: sub-network node}): this network without its categorical / dynamic ef-state nodes.  The
+        nodes under such an input become the inputs, one column each: the binary nodes get the one-hot observation
+        (categorical_state_prediction_error, prediction_error/categorical.py:36-45), the statistic-tracking nodes get t(x)
+        (prediction_error_update_exponential_family_dynamic, exponential.py:104-118); attributes are copied at call time."""
+        cats = set(self._vector_nodes())
         nodes = [i for i in range(self.n_nodes) if i not in cats]
         local = {g: k for k, g in enumerate(nodes)}
         sub = Network(volatility_updates=self.volatility_updates, max_posterior_precision=self.max_posterior_precision,
@@ -338,7 +357,13 @@ class Network:
                                          self.edges[g].coupling_fn) for g in nodes)
         sub.n_nodes = len(nodes)
         for g in nodes:
-            sub.attributes[local[g]] = deepcopy(self.attributes[g])
+            a = deepcopy(self.attributes[g])
+            for key, field in _EDGE_OF_KEY.items():  # coupling strengths of the edges that went with the removed nodes
+                members = getattr(self.edges[g], field)
+                if members is not None and a.get(key) is not None and any(j in cats for j in members):
+                    kept = [c for j, c in zip(members, np.atleast_1d(a[key])) if j not in cats]
+                    a[key] = np.asarray(kept, dtype=np.float64) if kept else None
+            sub.attributes[local[g]] = a
         sub.attributes[-1] = deepcopy(self.attributes[-1])
         inputs = []
         for g in self.input_idxs:
@@ -349,7 +374,7 @@ class Network:
     def _ef_nodes(self) -> list:
         """The ef-state nodes, after checking that the network is one this backend runs: the hgf_ef_filter path
         serves networks made of ef-state nodes only (they have no parents, so nothing couples them to HGF nodes)."""
-        ef = [i for i, e in enumerate(self.edges) if e.node_type == ef_state.NODE_TYPE]
+        ef = [i for i, e in enumerate(self.edges) if e.node_type == ef_state.NODE_TYPE and e.value_parents is None]
         if ef and len(ef) != len(self.edges):
             raise NotImplementedError("ef-state nodes and HGF nodes in one network: filter them as two networks")
         return ef
@@ -489,18 +514,21 @@ class Network:
             self.update_sequence = ((), tuple((i, "prediction_error_update_exponential_family_fixed") for i in self.input_idxs))
             self.scan_fn = True
             return self
-        cats = self._categorical_nodes()
-        if cats:  # the schedule of the implied nodes, framed by the categorical steps (get_update_sequence.py:301-305, 337-345)
+        cats = self._vector_nodes()
+        if cats:  # the schedule of the implied nodes, framed by the vector nodes' steps (get_update_sequence.py:282-305, 337-345)
             implied, local = self._implied_network()
             implied.create_belief_propagation_fn()
             back = {k: g for g, k in local.items()}
             seq = implied.update_sequence
-            self.input_dim = [int(self.attributes[i]["n_categories"]) if i in cats else 1 for i in self.input_idxs]
+            is_cat = lambda c: self.edges[c].node_type == categorical.NODE_TYPE  # noqa: E731
+            self.input_dim = [w for _, _, w in self._categorical_columns(None)]
             self.update_sequence = UpdateSequence(
                 tuple((back[i], f) for i, f in seq.prediction_steps),
-                tuple((c, categorical.categorical_state_prediction_error) for c in cats)
+                tuple((c, categorical.categorical_state_prediction_error if is_cat(c)
+                       else ef_state.prediction_error_update_exponential_family_dynamic) for c in cats)
                 + tuple((back[i], f) for i, f in seq.update_steps)
-                + tuple((c, categorical.categorical_state_update) for c in cats))
+                + tuple((c, categorical.categorical_state_update if is_cat(c)
+                         else ef_state.posterior_update_exponential_family_dynamic) for c in cats))
             self.scan_fn = True
             return self
         self.input_dim = [1 for _ in self.input_idxs]
@@ -763,7 +791,7 @@ class Network:
             self.create_belief_propagation_fn()
         if self._ef_nodes():
             return self._ef_input_data(input_data, time_steps, observed, record_trajectories)
-        if self._categorical_nodes():
+        if self._vector_nodes():
             return self._categorical_input_data(input_data, time_steps, observed)
         self._filter_one_series(input_data, time_steps, observed, record_trajectories)
         self._last_inputs = (input_data, time_steps, observed)
@@ -783,7 +811,7 @@ class Network:
             self.input_idxs = input_idxs
         if self.scan_fn is None:
             self.create_belief_propagation_fn()
-        if self._ef_nodes() or self._categorical_nodes():
+        if self._ef_nodes() or self._vector_nodes():
             raise NotImplementedError("input_custom_sequence serves binary-, continuous- and volatile-state networks")
         branches = tuple((tuple(b[0]), tuple(b[1])) for b in update_branches)
         if not 1 <= len(branches) <= _lib.MAX_BRANCHES:
@@ -847,10 +875,12 @@ class Network:
         """[(input node, first column, columns)] over the input nodes (get_input_dimension, network.py:1069-1086)."""
         out, col = [], 0
         for i in self.input_idxs:
-            d = int(self.attributes[i]["n_categories"]) if self.edges[i].node_type == categorical.NODE_TYPE else 1
+            kind = self.edges[i].node_type
+            d = int(self.attributes[i]["n_categories"]) if kind == categorical.NODE_TYPE else (
+                int(self.attributes[i]["dimension"]) if kind == ef_state.NODE_TYPE else 1)
             out.append((i, col, d))
             col += d
-        if n_columns != col:
+        if n_columns is not None and n_columns != col:
             raise ValueError(f"input_data has {n_columns} column(s) but the input nodes take {col}")
         return out
 
@@ -871,8 +901,12 @@ class Network:
                 per_node = [o] if o.ndim == 1 else [o[:, k] for k in range(o.shape[1])]
             masks = {i: per_node[j] for j, (i, _, _) in enumerate(cols)}
         implied, local = self._implied_network()
-        expanded = None if masks is None else np.stack([masks[i] for i, _, d in cols for _ in range(d)], axis=1)
-        implied.input_data(x, time_steps=time_steps, observed=expanded, record_trajectories=True)
+        # what the implied inputs are fed with: the raw columns, or t(x) for a dynamic ef-state node
+        is_ef = lambda i: self.edges[i].node_type == ef_state.NODE_TYPE  # noqa: E731
+        fed = [ef_state.sufficient_statistics(x[:, c0:c0 + d].astype(cast), d).astype(np.float64) if is_ef(i) else x[:, c0:c0 + d]
+               for i, c0, d in cols]
+        expanded = None if masks is None else np.stack([masks[i] for (i, _, _), f in zip(cols, fed) for _ in range(f.shape[1])], axis=1)
+        implied.input_data(np.concatenate(fed, axis=1), time_steps=time_steps, observed=expanded, record_trajectories=True)
         back = {k: g for g, k in local.items()}
         nt = {back[k]: v for k, v in implied.node_trajectories.items() if k != -1}
         nt[-1] = implied.node_trajectories[-1]
@@ -880,7 +914,26 @@ class Network:
         for k, g in back.items():
             last[g] = implied.last_attributes[k]
         last[-1] = implied.last_attributes[-1]
-        for c, c0, n in cols:
+        for (c, c0, n), ss in zip(cols, fed):
+            if is_ef(c):  # posterior_update_exponential_family_dynamic: per-step learning rate from the implied HGFs
+                a_nodes = self.edges[c].value_parents
+                b_nodes = [self.edges[a].value_parents[0] for a in a_nodes]
+                planes = [np.stack([nt[j][key] for j in group]) for group, key in
+                          ((a_nodes, "mean"), (a_nodes, "expected_mean"), (b_nodes, "mean"), (b_nodes, "expected_mean"))]
+                imp = torch.as_tensor(np.stack(planes)).to(device=dev, dtype=dt)[:, :, :, None].contiguous()  # [4][K][T][1]
+                obs = None if masks is None else torch.as_tensor((masks[c] != 0).astype(np.uint8)[None]).to(dev).contiguous()
+                series = torch.as_tensor(np.ascontiguousarray(x[None, :, c0:c0 + n])).to(device=dev, dtype=dt)
+                traj, fin, nus = ef_state.launch(bits=self.bits, device=dev, series=series, observed=obs, nus=None,
+                                                 xis0=self.attributes[c]["xis"], dimension=n, input_group_size=0,
+                                                 want_trajectory=True, implied=imp)
+                seen = np.ones(T, dtype=np.int64) if masks is None else (masks[c] != 0).astype(np.int64)
+                xc = x[:, c0:c0 + n].astype(cast)
+                nt[c] = {"dimension": np.full(T, n), "nus": nus[:, 0].cpu().numpy(), "xis": traj[:, :, 0].t().cpu().numpy(),
+                         "observed": seen, "mean": xc if n > 1 else xc[:, 0], "observation_ss": ss.astype(cast)}
+                if T:
+                    for key in ("nus", "xis", "observed", "mean", "observation_ss"):
+                        last[c][key] = nt[c][key][-1]
+                continue
             if self.edges[c].node_type != categorical.NODE_TYPE:
                 continue
             binary = self.edges[c].value_parents
@@ -908,7 +961,9 @@ class Network:
         """``batch`` with categorical nodes: the implied network's batch, then one hgf_categorical_update per node whose
         ``(node, "kl_divergence" | "surprise" | "alpha" | "mean")`` is recorded."""
         implied, local = self._implied_network()
-        cats = self._categorical_nodes()
+        cats = self._vector_nodes()
+        if any(self.edges[c].node_type == ef_state.NODE_TYPE for c in cats):
+            raise NotImplementedError("ef-state nodes with learning='hgf-*' are filtered through input_data on this path")
         own = [tuple(k) for k in record if k[0] in cats]
         if any(k[1] not in ("kl_divergence", "surprise", "alpha", "mean") for k in own):
             raise ValueError("a categorical node records 'kl_divergence', 'surprise', 'alpha' or 'mean'")
@@ -1265,7 +1320,7 @@ class Network:
             if response_function is not None or gradient or pointwise or fused_reduce is not None or time_steps is not None:
                 raise NotImplementedError("an ef-state network has no response function, gradient or time steps on this path")
             return self._ef_batch(input_data, parameters, observed, n_instances, input_group_size, record, last_attributes)
-        if self._categorical_nodes():
+        if self._vector_nodes():
             if response_function is not None or gradient or pointwise or fused_reduce is not None or last_attributes:
                 raise NotImplementedError("a network with categorical nodes batches trajectories (record=[...]) on this path")
             return self._categorical_batch(input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream)

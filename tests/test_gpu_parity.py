@@ -1085,3 +1085,38 @@ def test_categorical_batch(G):
         assert np.allclose(kl[i], one.node_trajectories[0]["kl_divergence"], rtol=1e-4, atol=1e-6)
         assert np.allclose(s[i], one.node_trajectories[0]["surprise"], rtol=1e-5)
         assert np.allclose(alpha[i], one.node_trajectories[0]["alpha"], rtol=1e-4)
+
+
+@pytest.mark.parametrize("learning,dtype", [("hgf-1", "float32"), ("hgf-2", "float32"), ("hgf-3", "float32"), ("hgf-2", "float64")])
+def test_ef_state_hgf_learning_matches_oracle(G, learning, dtype):
+    """learning='hgf-*' (tests/test_nodes/test_exponential_family.py:69-95 builds the hgf-2 network with these edits but
+    asserts nothing about it): the per-step learning rate implied by the statistic-tracking HGFs, against the oracle."""
+    from oracle import ef_state as ef
+
+    x = ef.spiral_data()[:300]
+    npd = np.float32 if dtype == "float32" else np.float64
+    stride = {"hgf-1": 2, "hgf-2": 3, "hgf-3": 4}[learning]
+    net = G.Network(dtype=dtype).add_nodes(kind="ef-state", learning=learning, distribution="multivariate-normal", dimension=2)
+
+    def edit(attributes, shift):  # the reference test's edits: B nodes' volatility, A nodes' precision, the covariance trackers' means
+        for k in range(5):
+            attributes[1 + stride * k + 1 - shift]["tonic_volatility"] = -2.0
+            attributes[1 + stride * k - shift]["precision"] = 0.01
+        for k in (2, 3, 4):
+            attributes[1 + stride * k + stride - 1 - shift]["mean"] = 10.0
+
+    edit(net.attributes, 0)
+    mask = np.arange(len(x)) % 11 != 5
+    net.input_data(x, observed=mask)
+    want = ef.ef_dynamic_filter(x, 2, "multivariate-normal", learning, edit=lambda o: edit(o.attributes, 1), observed=mask, dtype=npd)
+    got = net.node_trajectories[0]
+    assert got["xis"].shape == (300, 5) and got["nus"].shape == (300,) and np.isfinite(got["xis"]).all()
+    # nu divides differences of nearby numbers: its rounding is amplified, and xis inherits it through 1 / (1 + nu)
+    rt = 2e-3 if dtype == "float32" else 1e-8
+    # on an unobserved step the parents keep their predictions, so the expectation differential is 0 and nu is not finite
+    assert not np.isfinite(got["nus"][~mask]).any() and not np.isfinite(want["nus"][~mask]).any()
+    assert np.allclose(got["nus"][mask], want["nus"][mask], rtol=rt, atol=rt), np.abs(got["nus"][mask] - want["nus"][mask]).max()
+    assert np.allclose(got["xis"], want["xis"], rtol=rt, atol=rt)
+    assert np.array_equal(got["xis"][5], got["xis"][4])  # unobserved step: blank update
+    a_ref = want["network"].node_trajectories[0]["expected_mean"]
+    assert np.allclose(net.node_trajectories[1]["expected_mean"], a_ref, rtol=RTOL_TRAJ if dtype == "float32" else 1e-9, atol=1e-6)

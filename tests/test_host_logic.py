@@ -65,8 +65,22 @@ def test_ef_state_node_defaults(lib):
     assert m.input_idxs == (0,) and m.input_dim == [2]
     with pytest.raises(ValueError, match="either 'normal' or 'multivariate-normal'"):
         Network().add_nodes(kind="ef-state", distribution="gamma")
-    with pytest.raises(NotImplementedError, match="generalised-filtering"):
-        Network().add_nodes(kind="ef-state", learning="hgf-2")
+    with pytest.raises(ValueError, match="generalised-filtering"):
+        Network().add_nodes(kind="ef-state", learning="adam")
+    # learning="hgf-2" (add_nodes.py:438-452): per statistic a fed node, its value parent and a volatility parent of that;
+    # the node indexes the reference's test edits (tests/test_nodes/test_exponential_family.py:78-83) mean the same nodes
+    h = Network().add_nodes(kind="ef-state", learning="hgf-2", distribution="multivariate-normal", dimension=2)
+    assert len(h.edges) == 16 and h.edges[0].value_parents == (1, 4, 7, 10, 13)
+    assert h.edges[1].value_children == (0,) and h.edges[1].value_parents == (2,) and h.edges[2].volatility_parents == (3,)
+    assert len(Network().add_nodes(kind="ef-state", learning="hgf-1").edges) == 5
+    assert len(Network().add_nodes(kind="ef-state", learning="hgf-3").edges) == 9
+    h.create_belief_propagation_fn()
+    assert h.input_idxs == (0,) and h.input_dim == [2]
+    steps = [(i, f.__name__) for i, f in h.update_sequence.update_steps]
+    assert steps[0] == (0, "prediction_error_update_exponential_family_dynamic")
+    assert steps[-1] == (0, "posterior_update_exponential_family_dynamic")
+    implied, _ = h._implied_network()
+    assert implied.input_idxs == (0, 3, 6, 9, 12) and implied.attributes[0]["tonic_volatility"] == -4.0
     with pytest.raises(ValueError, match="not found in the default"):
         Network().add_nodes(kind="ef-state", tonic_volatility=-2.0)
     mixed = Network().add_nodes(kind="ef-state").add_nodes()
