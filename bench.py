@@ -132,14 +132,14 @@ def oracle_logp_grad(u, y, params, n_chains, n_threads=0):
 
 def cpu_baseline_leg(budget_s: float = 12.0):
     """Bounded sample of the headline workload on the host cores (oracle port, all threads)."""
-    cores = os.cpu_count() or 1
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     n_part = 8
     u, y, params = synth_config4(0, n_participants=n_part)
-    dt, _, _ = oracle_logp_grad(u, y, params, N_CHAINS)  # probe (also warms the library)
+    dt, _, _ = oracle_logp_grad(u, y, params, N_CHAINS, n_threads=cores)  # probe (also warms the library)
     per_part = max(dt / n_part, 1e-6)
     n_part = int(min(N_PARTICIPANTS, max(8, budget_s / per_part)))
     u, y, params = synth_config4(0, n_participants=n_part)
-    dt, _, _ = oracle_logp_grad(u, y, params, N_CHAINS)
+    dt, _, _ = oracle_logp_grad(u, y, params, N_CHAINS, n_threads=cores)
     n_inst = n_part * N_CHAINS
     return {"value": n_inst * N_TRIALS * N_NODES / dt, "unit": "node-updates/s", "cores": cores, "kind": "port",
             "sample": f"{n_part} participants x {N_CHAINS} chains x {N_TRIALS} trials logp+grad (Dual<double>, OpenMP), {dt:.2f} s",
@@ -153,16 +153,17 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; this arm is the CPU implementation with ALL host threads
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     n_part = 8
     u, y, params = synth_config4(0, n_participants=n_part)
-    dt, _, _ = oracle_logp_grad(u, y, params, N_CHAINS)
+    dt, _, _ = oracle_logp_grad(u, y, params, N_CHAINS, n_threads=cores)
     budget = 60.0 / max(1, args.steps + args.warmup)  # whole run within a few minutes
     n_part = int(min(N_PARTICIPANTS, max(8, min(budget, 8.0) / max(dt / n_part, 1e-6))))
     u, y, params = synth_config4(0, n_participants=n_part)
     for _ in range(args.warmup):
-        oracle_logp_grad(u, y, params, N_CHAINS)
-    times = [oracle_logp_grad(u, y, params, N_CHAINS)[0] for _ in range(args.steps)]
+        oracle_logp_grad(u, y, params, N_CHAINS, n_threads=cores)
+    times = [oracle_logp_grad(u, y, params, N_CHAINS, n_threads=cores)[0] for _ in range(args.steps)]
     total = float(sum(times))
     n_inst = n_part * N_CHAINS
     value = n_inst * N_TRIALS * N_NODES * args.steps / total
