@@ -477,6 +477,10 @@ class Network:
         Returns the kernel name the network's plans report afterwards."""
         from . import specialise as sp
 
+        if self._vector_nodes():  # the scan runs the implied network: that is the topology to specialise
+            if self.scan_fn is None:
+                self.create_belief_propagation_fn()
+            return self._implied_network()[0].specialise(gradient_parameters, response_parameter, float64, verbose)
         kernels = [(0, 0)]
         if gradient_parameters or response_parameter:
             kernels.append((min(int(gradient_parameters), 4), 1 if response_parameter else 0))
