@@ -1120,3 +1120,26 @@ def test_ef_state_hgf_learning_matches_oracle(G, learning, dtype):
     assert np.array_equal(got["xis"][5], got["xis"][4])  # unobserved step: blank update
     a_ref = want["network"].node_trajectories[0]["expected_mean"]
     assert np.allclose(net.node_trajectories[1]["expected_mean"], a_ref, rtol=RTOL_TRAJ if dtype == "float32" else 1e-9, atol=1e-6)
+
+
+def test_vector_nodes_against_committed_vectors(G):
+    """Categorical and ef-state nodes against tests/golden/vector_nodes.npz; no oracle code runs in this test."""
+    import os
+
+    v = np.load(os.path.join(os.path.dirname(__file__), "golden", "vector_nodes.npz"))
+    for name, n in (("reference3", 3), ("five", 5)):
+        for dtype, amp in (("float32", 1e-3), ("float64", 1e-7)):
+            net = G.Network(dtype=dtype).add_nodes(kind="categorical-state", node_parameters={"n_categories": n})
+            got = net.input_data(v[f"categorical/{name}/x"]).node_trajectories[0]
+            assert np.allclose(got["alpha"], v[f"categorical/{name}/{dtype}/alpha"], rtol=amp)
+            assert np.allclose(got["surprise"], v[f"categorical/{name}/{dtype}/surprise"], rtol=RTOL_SUM if dtype == "float32" else 1e-9)
+            assert np.allclose(got["kl_divergence"], v[f"categorical/{name}/{dtype}/kl_divergence"], rtol=10 * amp, atol=amp)
+    x = v["ef/spiral"]
+    for dtype, rt in (("float32", RTOL_TRAJ), ("float64", 1e-12)):
+        net = G.Network(dtype=dtype).add_nodes(kind="ef-state", distribution="multivariate-normal", dimension=2).input_data(x)
+        assert np.allclose(net.node_trajectories[0]["xis"], v[f"ef/fixed/{dtype}/xis"], rtol=rt, atol=rt)
+    uni = G.Network(dtype="float64").add_nodes(kind="ef-state", nus=7.5).input_data(x[:, 0])
+    assert np.allclose(uni.node_trajectories[0]["xis"], v["ef/fixed_univariate/float64/xis"], rtol=1e-12)
+    dyn = G.Network(dtype="float64").add_nodes(kind="ef-state", learning="hgf-2", distribution="multivariate-normal", dimension=2)
+    got = dyn.input_data(x[:300]).node_trajectories[0]
+    assert np.allclose(got["nus"], v["ef/hgf2/float64/nus"], rtol=1e-8) and np.allclose(got["xis"], v["ef/hgf2/float64/xis"], rtol=1e-8)

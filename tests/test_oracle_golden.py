@@ -491,3 +491,21 @@ def test_categorical_state_node_golden():
     assert np.allclose(c["alpha"], c64["alpha"], rtol=1e-4) and (c64["alpha"] > 0).all()
     _, other = cat.categorical_filter(x, 3, {"tonic_volatility_2": -2.0}, dtype="float32")
     assert not np.isclose(other["surprise"].sum(), 12.418026)  # the override would change the answer
+
+
+def test_vector_node_restatements_reproduce_the_committed_vectors():
+    """tests/golden/vector_nodes.npz (tests/golden/make_vector_node_vectors.py) against the restatements as they are now."""
+    import os
+
+    from oracle import categorical as cat
+    from oracle import ef_state as ef
+
+    v = np.load(os.path.join(os.path.dirname(__file__), "golden", "vector_nodes.npz"))
+    assert np.isclose(v["categorical/reference3/float32/kl_divergence"].sum(), 1.2642910)
+    assert np.isclose(v["categorical/reference3/float32/surprise"].sum(), 12.418026)
+    assert np.isclose(v["ef/fixed/float32/xis"][-1], [3.4652710e01, -1.0609777e00, 1.2103647e03, -3.6398651e01, 3.3951855e00]).all()
+    _, c = cat.categorical_filter(v["categorical/five/x"], 5, None, dtype="float64")
+    assert np.allclose(c["kl_divergence"], v["categorical/five/float64/kl_divergence"], rtol=1e-12)
+    assert np.allclose(ef.ef_filter(v["ef/spiral"], 3.0, 2, "multivariate-normal", dtype=np.float64), v["ef/fixed/float64/xis"], rtol=1e-13)
+    d = ef.ef_dynamic_filter(v["ef/spiral"][:300], 2, "multivariate-normal", "hgf-2", dtype=np.float64)
+    assert np.allclose(d["nus"], v["ef/hgf2/float64/nus"], rtol=1e-10, equal_nan=True)
