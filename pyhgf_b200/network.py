@@ -962,48 +962,85 @@ class Network:
         return self
 
     def _categorical_batch(self, input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream):
-        """``batch`` with categorical nodes: the implied network's batch, then one hgf_categorical_update per node whose
-        ``(node, "kl_divergence" | "surprise" | "alpha" | "mean")`` is recorded."""
+        """``batch`` with categorical / dynamic ef-state nodes: the implied network's batch (fed with the one-hot columns
+        or with t(x)), then one launch per vector node that is recorded -- ``(node, "kl_divergence" | "surprise" |
+        "alpha" | "mean")`` for a categorical node, ``(node, "xis" | "nus")`` for an ef-state node."""
         implied, local = self._implied_network()
         cats = self._vector_nodes()
-        if any(self.edges[c].node_type == ef_state.NODE_TYPE for c in cats):
-            raise NotImplementedError("ef-state nodes with learning='hgf-*' are filtered through input_data on this path")
+        is_ef = lambda c: self.edges[c].node_type == ef_state.NODE_TYPE  # noqa: E731
         own = [tuple(k) for k in record if k[0] in cats]
-        if any(k[1] not in ("kl_divergence", "surprise", "alpha", "mean") for k in own):
-            raise ValueError("a categorical node records 'kl_divergence', 'surprise', 'alpha' or 'mean'")
+        for k in own:
+            allowed = ("xis", "nus") if is_ef(k[0]) else ("kl_divergence", "surprise", "alpha", "mean")
+            if k[1] not in allowed:
+                raise ValueError(f"node {k[0]} records one of {allowed}")
         params = {}
         for k, v in parameters.items():
             if isinstance(k, (tuple, list)) and isinstance(k[0], (int, np.integer)) and k[0] >= 0:
                 if k[0] in cats:
-                    raise ValueError("the parameters of a categorical node's binary HGFs live on the implied nodes")
+                    raise ValueError("per-instance parameters live on the nodes implied under a categorical / ef-state node")
                 params[(local[k[0]],) + tuple(k[1:])] = v
             else:
                 params[k] = v
         rec = [(local[k[0]],) + tuple(k[1:]) for k in record if k[0] not in cats]
         needed = {}
         for c in sorted({k[0] for k in own}):
-            binary = self.edges[c].value_parents
-            needed[c] = ([(local[b], "expected_mean") for b in binary], [(local[self.edges[b].value_parents[0]], "mean") for b in binary])
-        extra = [k for pair in needed.values() for group in pair for k in group if k not in rec]
-        if observed is not None:
-            raise NotImplementedError("observation masks with categorical nodes go through input_data")
-        res = implied.batch(input_data, params, time_steps=time_steps, n_instances=n_instances, input_group_size=input_group_size,
-                            record=rec + list(dict.fromkeys(extra)), stream=stream)
-        traj = res.trajectories
+            under = self.edges[c].value_parents
+            above = [self.edges[b].value_parents[0] for b in under]
+            if is_ef(c):  # hgf_ef_call_t::implied: A.mean, A.expected_mean, B.mean, B.expected_mean
+                needed[c] = tuple([(local[j], key) for j in group] for group, key in
+                                  ((under, "mean"), (under, "expected_mean"), (above, "mean"), (above, "expected_mean")))
+            else:
+                needed[c] = ([(local[b], "expected_mean") for b in under], [(local[p], "mean") for p in above])
+        extra = [k for groups in needed.values() for group in groups for k in group if k not in rec]
         dev, dt = self.device, _torch_dtype(self.bits)
+        grouped = input_group_size > 0
         x = torch.as_tensor(np.asarray(input_data) if not torch.is_tensor(input_data) else input_data).to(device=dev, dtype=dt)
-        x = x[None] if input_group_size <= 0 else x
-        cols = {i: (c0, d) for i, c0, d in self._categorical_columns(x.shape[2])}
+        if not grouped:
+            x = (x[:, None] if x.ndim == 1 else x)[None]
+        elif x.ndim == 2:
+            x = x[:, :, None]
+        cols = self._categorical_columns(x.shape[2])
+        fed = []
+        for i, c0, d in cols:  # what the implied inputs observe: the raw columns, or t(x) for an ef-state node
+            part = x[:, :, c0:c0 + d]
+            if is_ef(i):
+                r_, q_ = np.tril_indices(d)
+                part = torch.cat([part, part[:, :, r_.tolist()] * part[:, :, q_.tolist()]], dim=2)
+            fed.append(part)
+        widths = [f.shape[2] for f in fed]
+        fed = torch.cat(fed, dim=2).contiguous()
+        masks = None
+        if observed is not None:  # one mask column per input node -> one per implied input
+            o = torch.as_tensor(np.asarray(observed) if not torch.is_tensor(observed) else observed).to(dev)
+            o = o.reshape(x.shape[0], x.shape[1], -1)
+            if o.shape[2] != len(cols):
+                raise ValueError(f"observed has {o.shape[2]} column(s) for {len(cols)} input node(s)")
+            masks = {i: (o[:, :, j] != 0).to(torch.uint8).contiguous() for j, (i, _, _) in enumerate(cols)}
+            observed = torch.cat([masks[i][:, :, None].expand(-1, -1, w) for (i, _, _), w in zip(cols, widths)], dim=2)
+            observed = observed if grouped else observed[0]
+        res = implied.batch(fed if grouped else fed[0], params, time_steps=time_steps, observed=observed, n_instances=n_instances,
+                            input_group_size=input_group_size, record=rec + list(dict.fromkeys(extra)), stream=stream)
+        traj = res.trajectories
+        where = {i: (c0, d) for i, c0, d in cols}
         back = {k: g for g, k in local.items()}
         out = {(back[k[0]],) + tuple(k[1:]): v for k, v in traj.items() if k in rec}
-        for c, (em_keys, pm_keys) in needed.items():
-            c0, n = cols[c]
-            em = torch.stack([traj[k].t() for k in em_keys]).contiguous()  # [n][T][N]
-            pm = torch.stack([traj[k].t() for k in pm_keys]).contiguous()
+        for c, groups in needed.items():
+            c0, n = where[c]
+            planes = [torch.stack([traj[k].t() for k in group]) for group in groups]  # each [n or K][T][N]
+            if is_ef(c):
+                xt, _, nus = ef_state.launch(bits=self.bits, device=dev, series=x[:, :, c0:c0 + n].contiguous(),
+                                             observed=None if masks is None else masks[c], nus=None, xis0=self.attributes[c]["xis"],
+                                             dimension=n, input_group_size=input_group_size,
+                                             want_trajectory=(c, "xis") in own, implied=torch.stack(planes).contiguous())
+                if (c, "xis") in own:
+                    out[(c, "xis")] = xt.permute(2, 1, 0)  # [N][T][K] view of the kernel's [K][T][N]
+                if (c, "nus") in own:
+                    out[(c, "nus")] = nus.t()
+                continue
             want_vec = any(k[0] == c and k[1] in ("alpha", "mean") for k in own)
-            r = categorical.update(bits=self.bits, device=dev, observations=x[:, :, c0:c0 + n].contiguous(), expected_mean=em,
-                                   parent_mean=pm, alpha0=self.attributes[c]["alpha"], input_group_size=input_group_size,
-                                   want_vectors=want_vec)
+            r = categorical.update(bits=self.bits, device=dev, observations=x[:, :, c0:c0 + n].contiguous(),
+                                   expected_mean=planes[0].contiguous(), parent_mean=planes[1].contiguous(),
+                                   alpha0=self.attributes[c]["alpha"], input_group_size=input_group_size, want_vectors=want_vec)
             for k in own:
                 if k[0] == c:
                     out[k] = r[k[1]].t() if k[1] in ("kl_divergence", "surprise") else r[k[1]].permute(2, 1, 0)

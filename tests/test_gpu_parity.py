@@ -1143,3 +1143,39 @@ def test_vector_nodes_against_committed_vectors(G):
     dyn = G.Network(dtype="float64").add_nodes(kind="ef-state", learning="hgf-2", distribution="multivariate-normal", dimension=2)
     got = dyn.input_data(x[:300]).node_trajectories[0]
     assert np.allclose(got["nus"], v["ef/hgf2/float64/nus"], rtol=1e-8) and np.allclose(got["xis"], v["ef/hgf2/float64/xis"], rtol=1e-8)
+
+
+def test_vector_nodes_batch_masks_and_dynamic_ef(G):
+    """Network.batch with an observation mask (categorical) and with a dynamic ef-state node: per-instance results equal
+    the single-series runs with the same attributes."""
+    from oracle import ef_state as ef
+
+    rng = np.random.default_rng(21)
+    n, N, T = 3, 70, 40
+    x = rng.multinomial(1, [0.2, 0.3, 0.5], size=T).astype(float)
+    mask = (rng.random(T) > 0.25).astype(int)
+    om = rng.uniform(-5.0, -2.5, N)
+    net = G.Network().add_nodes(kind="categorical-state", node_parameters={"n_categories": n})
+    r = net.batch(x, {(1 + n + k, "tonic_volatility"): om for k in range(n)}, observed=mask, record=[(0, "surprise"), (0, "alpha")])
+    for i in (0, 33, 69):
+        one = G.Network().add_nodes(kind="categorical-state", node_parameters={"n_categories": n})
+        for k in range(n):
+            one.attributes[1 + n + k]["tonic_volatility"] = float(om[i])
+        one.input_data(x, observed=mask)
+        assert np.allclose(r.trajectories[(0, "surprise")][i].cpu().numpy(), one.node_trajectories[0]["surprise"], rtol=1e-5)
+        assert np.allclose(r.trajectories[(0, "alpha")][i].cpu().numpy(), one.node_trajectories[0]["alpha"], rtol=1e-4, equal_nan=True)
+
+    xs = ef.spiral_data()[:120]
+    om_b = rng.uniform(-4.0, -1.5, 48)
+    dyn = G.Network(dtype="float64").add_nodes(kind="ef-state", learning="hgf-2", distribution="multivariate-normal", dimension=2)
+    b_nodes = [2, 5, 8, 11, 14]
+    rb = dyn.batch(xs, {(b, "tonic_volatility"): om_b for b in b_nodes}, record=[(0, "xis"), (0, "nus"), (1, "expected_mean")])
+    assert rb.trajectories[(0, "xis")].shape == (48, 120, 5) and rb.trajectories[(0, "nus")].shape == (48, 120)
+    for i in (0, 20, 47):
+        one = G.Network(dtype="float64").add_nodes(kind="ef-state", learning="hgf-2", distribution="multivariate-normal", dimension=2)
+        for b in b_nodes:
+            one.attributes[b]["tonic_volatility"] = float(om_b[i])
+        one.input_data(xs)
+        assert np.allclose(rb.trajectories[(0, "xis")][i].cpu().numpy(), one.node_trajectories[0]["xis"], rtol=1e-9)
+        assert np.allclose(rb.trajectories[(0, "nus")][i].cpu().numpy(), one.node_trajectories[0]["nus"], rtol=1e-9)
+        assert np.allclose(rb.trajectories[(1, "expected_mean")][i].cpu().numpy(), one.node_trajectories[1]["expected_mean"], rtol=1e-10)
