@@ -12,20 +12,44 @@
 // Literal semantics follow the reference's weak-typed Python scalars: a literal
 // adopts the array dtype, so `1e-128` is 0.0f in float32.
 //
-// Math policy (float32 only; float64 always uses IEEE division and libdevice):
-//   default            -- SFU primitives: division = MUFU.RCP x multiply, exp = MUFU.EX2,
-//                         log = MUFU.LG2 (<= 2 ulp each), mul+add contraction allowed.  This is
-//                         what makes the time loop SFU/FP32-pipe bound instead of instruction bound;
-//                         parity with the reference stays inside the stated tolerances
-//                         (tests/test_gpu_parity.py).
-//   -DHGF_MATH_ACCURATE -- IEEE division, libdevice expf/logf/log1pf/powf and -fmad=false
-//                         (one rounding per primitive, the oracle's arithmetic): the validation
-//                         build, `HGF_MATH=accurate python -m pyhgf_b200.build`.
+// Math policy (float32 device code only; float64 and host code always use IEEE division and libm/libdevice).
+// Four independent knobs, one per primitive class, chosen at compile time (-DHGF_<X>_MODE=n); what the shipped
+// library uses, and what each costs in parity and time, is measured by tools/parity_ablation.py
+// (profiles/r2_parity_ablation.json):
+//   HGF_DIV_MODE  0  a * MUFU.RCP(b)                      (2 roundings, <= 2 ulp)
+//                 1  MUFU.RCP + one Newton step on the quotient (2 FMA + NaN guard; <= 1 ulp, special values kept)
+//                 2  IEEE division (div.rn)
+//   HGF_EXP_MODE  0  MUFU.EX2(x * log2 e)                 (argument rounding: relative error ~ |x| 2^-24, + 2 ulp)
+//                 2  libdevice expf (Cody-Waite reduction around the same MUFU.EX2, <= 2 ulp over the whole range)
+//   HGF_LOG_MODE  0  MUFU.LG2(x) * ln 2, log1p(x) = log(1 + x)   (absolute error 2^-22 near 1)
+//                 1  libdevice logf; log1p(x) = logf(u) + (x - (u - 1)) / u with u = 1 + x (first-order repair of the
+//                    rounding of 1 + x: one MUFU.RCP instead of log1pf's second polynomial)
+//                 2  libdevice logf and log1pf
+//   HGF_POW_MODE  0  MUFU.EX2(y * MUFU.LG2(x))            (only the inverse-temperature response uses pow; its
+//                 2  libdevice powf                         result does not feed back into the beliefs)
+//   HGF_FTZ       1  the MUFU wrappers flush subnormals (.ftz); 0: they do not
+//   HGF_RESP_MODE 0  the response functions and the binary node's sigmoid follow the knobs above
+//                 1  libdevice powf + an IEEE-accurate quotient in the inverse-temperature response, an IEEE-accurate
+//                    reciprocal in the binary node's sigmoid: a probability next to 1 whose complement is taken
+//                    afterwards (-log(1 - p)) needs its LAST BIT -- one ulp of p is per cents of 1 - p ~ 1e-6
+//                 2  the same, but powf only when a lane of the warp is in that regime (warp-uniform branch)
+// Shipped: DIV/EXP/LOG/POW = 0, FTZ = 1, RESP = 2.  Measured (profiles/r2_parity_ablation.json): RESP is what the
+// round-1 build lacked (260 of 32 768 instances of the omega in [-6, -3] box off by more than 1e-4, 3-6 with it --
+// the same count, and mostly the same instances, as the all-IEEE validation build, which is 2.7x slower); making
+// division, exp or log more accurate on top of it changes nothing measurable and costs 13-29 % each.
+// Tangent (derivative) arithmetic has no rounding contract with the reference: it always takes MUFU.RCP
+// reciprocals and explicit FMAs, except under -DHGF_MATH_ACCURATE.
+//   -DHGF_MATH_ACCURATE -- every knob at 2, IEEE reciprocals for the tangents too, and (build.py) -fmad=false:
+//                         one rounding per primitive, the oracle's arithmetic.  The validation build,
+//                         `HGF_MATH=accurate python -m pyhgf_b200.build`.
 // Kernels never instantiate a bare float: the plain filter runs on Dual<B, 0>, so every
 // operator below -- in particular operator/ -- is ours.
 #pragma once
 #include <cuda_runtime.h>
 #include <math_constants.h>
+#ifndef __CUDACC__
+#include <math.h>  // a plain C++ compiler (tools/hostsim) does not get the math functions from cuda_runtime.h
+#endif
 
 #define HGF_HD __host__ __device__ __forceinline__
 // The update equations are also compilable for the host: tests/ builds them into a
@@ -58,33 +82,155 @@ template <class T> struct scalar_traits { using base = T; static constexpr int n
 template <class B, int P> struct scalar_traits<Dual<B, P>> { using base = B; static constexpr int n_tangents = P; };
 template <class T> using base_t = typename scalar_traits<T>::base;
 
-// The library is compiled with -fmad=false so that primal arithmetic rounds once per operation like the
-// reference's; derivative (tangent) arithmetic has no such contract and uses fused multiply-adds explicitly.
+// Tangent arithmetic uses fused multiply-adds explicitly (the primal's contraction is the compiler's: on in the
+// shipped build, off with -fmad=false in the validation build).
 HGF_HD float b_fma(float a, float b, float c) { return ::fmaf(a, b, c); }
 HGF_HD double b_fma(double a, double b, double c) { return ::fma(a, b, c); }
 
-#if defined(__CUDA_ARCH__) && !defined(HGF_MATH_ACCURATE)
-#define HGF_SFU_MATH 1
+#ifdef HGF_MATH_ACCURATE
+#undef HGF_DIV_MODE
+#undef HGF_EXP_MODE
+#undef HGF_LOG_MODE
+#undef HGF_POW_MODE
+#define HGF_DIV_MODE 2
+#define HGF_EXP_MODE 2
+#define HGF_LOG_MODE 2
+#define HGF_POW_MODE 2
 #endif
-// reciprocal and division
-HGF_HD float b_rcp(float x) {
-#ifdef HGF_SFU_MATH
-  float r;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-  return r;
+#if !defined(__CUDA_ARCH__) && !defined(HGF_HOST_EMULATE_SFU)  // host compilation of the equations: IEEE / libm throughout
+#undef HGF_DIV_MODE
+#undef HGF_EXP_MODE
+#undef HGF_LOG_MODE
+#undef HGF_POW_MODE
+#define HGF_DIV_MODE 2
+#define HGF_EXP_MODE 2
+#define HGF_LOG_MODE 2
+#define HGF_POW_MODE 2
+#endif
+#ifndef HGF_DIV_MODE
+#define HGF_DIV_MODE 0
+#endif
+#ifndef HGF_EXP_MODE
+#define HGF_EXP_MODE 0
+#endif
+#ifndef HGF_LOG_MODE
+#define HGF_LOG_MODE 0
+#endif
+#ifndef HGF_POW_MODE
+#define HGF_POW_MODE 0
+#endif
+#ifndef HGF_FTZ
+#define HGF_FTZ 1
+#endif
+#ifndef HGF_RESP_MODE  // last-bit arithmetic for probabilities whose complement is taken: hgf_ops.cuh, response_step
+#define HGF_RESP_MODE 2
+#endif
+#if defined(__CUDA_ARCH__) && !defined(HGF_MATH_ACCURATE)
+#define HGF_SFU_TANGENTS 1  // tangents take MUFU.RCP reciprocals
+#endif
+
+// raw SFU primitives (device only)
+#ifdef __CUDA_ARCH__
+#if HGF_FTZ
+HGF_D float sfu_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+HGF_D float sfu_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+HGF_D float sfu_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#else
+HGF_D float sfu_rcp(float x) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+HGF_D float sfu_ex2(float x) { float r; asm("ex2.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+HGF_D float sfu_lg2(float x) { float r; asm("lg2.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#endif
+#elif defined(HGF_HOST_EMULATE_SFU)
+// tools/hostsim: the SFU primitives EMULATED on the host for numerics experiments without a GPU -- the correctly
+// rounded result moved by a deterministic pseudo-random amount inside the documented error bound of the PTX
+// instruction (rcp.approx 1 ulp; ex2.approx 2 ulp; lg2.approx 2^-22 absolute in (0.5, 2), relative elsewhere).
+// Like the hardware it is a pure function of the input bits; it is NOT the hardware's function.
+static inline float sfu_emu_jitter(float x) {  // in [-1, 1)
+  unsigned u; __builtin_memcpy(&u, &x, 4);
+  u ^= u >> 16; u *= 0x7feb352du; u ^= u >> 15; u *= 0x846ca68bu; u ^= u >> 16;
+  return static_cast<float>(static_cast<int>(u >> 8) - (1 << 23)) * (1.0f / (1 << 23));
+}
+static inline float sfu_emu_rel(double exact, float key, double ulps) {
+  const float r = static_cast<float>(exact);
+  if (!(__builtin_fabsf(r) < 3.0e38f) || r == 0.0f) return r;
+  return static_cast<float>(exact * (1.0 + ulps * 5.9604645e-8 * sfu_emu_jitter(key)));
+}
+static inline float sfu_rcp(float x) { return sfu_emu_rel(1.0 / static_cast<double>(x), x, 1.0); }
+static inline float sfu_ex2(float x) { return sfu_emu_rel(::exp2(static_cast<double>(x)), x, 2.0); }
+static inline float sfu_lg2(float x) {
+  const double e = ::log2(static_cast<double>(x));
+  if (x > 0.5f && x < 2.0f) return static_cast<float>(e + 2.3841858e-7 * sfu_emu_jitter(x));
+  return sfu_emu_rel(e, x, 4.0);
+}
+#define HGF_SFU_TANGENTS 1
+#else
+HGF_D float sfu_rcp(float x) { return 1.0f / x; }
+#endif
+
+// reciprocal of a tangent-grade quantity
+HGF_HD float t_rcp(float x) {
+#ifdef HGF_SFU_TANGENTS
+  return sfu_rcp(x);
 #else
   return 1.0f / x;
 #endif
 }
-HGF_HD double b_rcp(double x) { return 1.0 / x; }
-HGF_HD float b_div(float a, float b) {
-#ifdef HGF_SFU_MATH
-  return a * b_rcp(b);
+HGF_HD double t_rcp(double x) { return 1.0 / x; }
+
+// a / b given r0 = sfu_rcp(b): the primal's division under the policy
+HGF_HD float div_from_rcp(float a, float b, float r0) {
+#if HGF_DIV_MODE == 0
+  (void)b;
+  return a * r0;
+#elif HGF_DIV_MODE == 1
+  // one Newton step on the quotient; the residual is NaN exactly where q is already the answer (b = 0, inf;
+  // q overflowed), so a NaN refinement falls back to q and special values flow as they do in a true division
+  const float q = a * r0;
+  const float q1 = ::fmaf(::fmaf(-b, q, a), r0, q);
+  return (q1 == q1) ? q1 : q;
 #else
+  (void)r0;
   return a / b;
 #endif
 }
+HGF_HD float b_rcp(float x) {
+#if HGF_DIV_MODE == 2
+  return 1.0f / x;
+#else
+  return div_from_rcp(1.0f, x, sfu_rcp(x));
+#endif
+}
+HGF_HD double b_rcp(double x) { return 1.0 / x; }
+HGF_HD float b_div(float a, float b) {
+#if HGF_DIV_MODE == 2
+  return a / b;
+#else
+  return div_from_rcp(a, b, sfu_rcp(b));
+#endif
+}
 HGF_HD double b_div(double a, double b) { return a / b; }
+// a / b to IEEE accuracy whatever the policy (MUFU.RCP + Newton step, or div.rn): for the few quotients whose
+// LAST BIT matters -- a probability next to 1 whose complement is taken afterwards (1 - p), see the response
+// functions in hgf_ops.cuh.  On this path's data the Newton form returned the IEEE quotient everywhere
+// (profiles/r2_parity_ablation.json: div1 == div2 to the last digit).
+HGF_HD float exact_div_from_rcp(float a, float b, float r0) {
+#if HGF_DIV_MODE == 2
+  (void)r0;
+  return a / b;
+#else
+  const float q = a * r0;
+  const float q1 = ::fmaf(::fmaf(-b, q, a), r0, q);
+  return (q1 == q1) ? q1 : q;
+#endif
+}
+HGF_HD float exact_rcp(float x) {
+#if HGF_DIV_MODE == 2
+  return 1.0f / x;
+#else
+  return exact_div_from_rcp(1.0f, x, sfu_rcp(x));
+#endif
+}
+HGF_HD double exact_rcp(double x) { return 1.0 / x; }
 
 HGF_HD float pv(float x) { return x; }
 HGF_HD double pv(double x) { return x; }
@@ -116,18 +262,45 @@ template <class B, int P> HGF_HD Dual<B, P> operator*(const Dual<B, P>& a, const
   for (int i = 0; i < P; ++i) r.d[i] = b_fma(a.d[i], b.v, a.v * b.d[i]);
   return r;
 }
+// a / b for the primal of a Dual, and the tangent-grade reciprocal of b for its derivative: with the SFU
+// policies both come from ONE MUFU.RCP; `tangents(inv)` is only run when the Dual carries tangents.
+template <class F> HGF_HD void dual_div_primal(float a, float b, float& q, bool has_tangents, F tangents) {
+#if defined(HGF_SFU_TANGENTS) && HGF_DIV_MODE != 2
+  const float r0 = sfu_rcp(b);
+  q = div_from_rcp(a, b, r0);
+  if (has_tangents) tangents(r0);
+#else
+  q = b_div(a, b);
+  if (has_tangents) tangents(t_rcp(b));
+#endif
+}
+template <class F> HGF_HD void dual_div_primal(double a, double b, double& q, bool has_tangents, F tangents) {
+  q = a / b;
+  if (has_tangents) tangents(1.0 / b);
+}
 template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, const Dual<B, P>& b) {
   Dual<B, P> r;
-  const B inv = b_rcp(b.v);
-#ifdef HGF_SFU_MATH
-  r.v = a.v * inv;
+  dual_div_primal(a.v, b.v, r.v, P > 0, [&](B inv) {
+#pragma unroll
+    for (int i = 0; i < P; ++i) r.d[i] = b_fma(-r.v, b.d[i], a.d[i]) * inv;
+  });
+  return r;
+}
+// a / b with the primal quotient at IEEE accuracy under every policy (see exact_div_from_rcp)
+template <int P> HGF_HD Dual<float, P> exact_div(const Dual<float, P>& a, const Dual<float, P>& b) {
+  Dual<float, P> r;
+#if defined(HGF_SFU_TANGENTS) && HGF_DIV_MODE != 2
+  const float inv = sfu_rcp(b.v);
+  r.v = exact_div_from_rcp(a.v, b.v, inv);
 #else
-  r.v = b_div(a.v, b.v);
+  const float inv = t_rcp(b.v);
+  r.v = a.v / b.v;
 #endif
 #pragma unroll
   for (int i = 0; i < P; ++i) r.d[i] = b_fma(-r.v, b.d[i], a.d[i]) * inv;
   return r;
 }
+template <int P> HGF_HD Dual<double, P> exact_div(const Dual<double, P>& a, const Dual<double, P>& b) { return a / b; }
 // scalar (tangent-free) operands
 template <class B, int P> HGF_HD Dual<B, P> operator+(const Dual<B, P>& a, B b) { Dual<B, P> r = a; r.v = a.v + b; return r; }
 template <class B, int P> HGF_HD Dual<B, P> operator+(B a, const Dual<B, P>& b) { Dual<B, P> r = b; r.v = a + b.v; return r; }
@@ -141,47 +314,61 @@ template <class B, int P> HGF_HD Dual<B, P> operator*(const Dual<B, P>& a, B b) 
 }
 template <class B, int P> HGF_HD Dual<B, P> operator*(B a, const Dual<B, P>& b) { return b * a; }
 template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, B b) {
-  Dual<B, P> r; r.v = b_div(a.v, b);
-  if constexpr (P > 0) {
-    const B inv = b_rcp(b);
+  Dual<B, P> r;
+  dual_div_primal(a.v, b, r.v, P > 0, [&](B inv) {
 #pragma unroll
     for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
-  }
+  });
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator/(B a, const Dual<B, P>& b) {
   Dual<B, P> r;
-  const B inv = b_rcp(b.v);
-#ifdef HGF_SFU_MATH
-  r.v = a * inv;
-#else
-  r.v = b_div(a, b.v);
-#endif
-  if constexpr (P > 0) {
+  dual_div_primal(a, b.v, r.v, P > 0, [&](B inv) {
     const B c = -r.v * inv;
 #pragma unroll
     for (int i = 0; i < P; ++i) r.d[i] = c * b.d[i];
-  }
+  });
   return r;
 }
 
 // ----------------------------------------------------------------------------
-// Elementary functions (float32: SFU primitives by default, libdevice with
-// -DHGF_MATH_ACCURATE; see the math policy at the top of this file)
+// Elementary functions (float32: see the math policy at the top of this file)
 // ----------------------------------------------------------------------------
-#ifdef HGF_SFU_MATH
-HGF_D float sfu_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-HGF_D float sfu_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-HGF_D float b_exp(float x) { return sfu_ex2(x * 1.4426950408889634f); }
-HGF_D float b_log(float x) { return sfu_lg2(x) * 0.6931471805599453f; }
-HGF_D float b_log1p(float x) { return b_log(1.0f + x); }
-HGF_D float b_pow(float x, float y) { return sfu_ex2(y * sfu_lg2(x)); }
+HGF_D float b_exp(float x) {
+#if HGF_EXP_MODE == 0
+  return sfu_ex2(x * 1.4426950408889634f);
 #else
-HGF_D float b_exp(float x) { return ::expf(x); }
-HGF_D float b_log(float x) { return ::logf(x); }
-HGF_D float b_log1p(float x) { return ::log1pf(x); }
-HGF_D float b_pow(float x, float y) { return ::powf(x, y); }
+  return ::expf(x);
 #endif
+}
+HGF_D float b_log(float x) {
+#if HGF_LOG_MODE == 0
+  return sfu_lg2(x) * 0.6931471805599453f;
+#else
+  return ::logf(x);
+#endif
+}
+HGF_D float b_log1p(float x) {
+#if HGF_LOG_MODE == 0
+  return b_log(1.0f + x);
+#elif HGF_LOG_MODE == 1
+  // log(u) + (x - (u - 1)) / u, u = fl(1 + x): repairs the rounding of 1 + x to first order.  u - 1 is exact for
+  // x >= -1/2 (Sterbenz) -- the only caller, logaddexp, passes x in [0, 1].  An infinite or NaN x gives log(u).
+  const float u = 1.0f + x;
+  const float l = ::logf(u);
+  const float c = (x - (u - 1.0f)) * sfu_rcp(u);
+  return (c == c) ? l + c : l;
+#else
+  return ::log1pf(x);
+#endif
+}
+HGF_D float b_pow(float x, float y) {
+#if HGF_POW_MODE == 0
+  return sfu_ex2(y * sfu_lg2(x));
+#else
+  return ::powf(x, y);
+#endif
+}
 HGF_D double b_exp(double x) { return ::exp(x); }
 HGF_D double b_log(double x) { return ::log(x); }
 HGF_D double b_log1p(double x) { return ::log1p(x); }
@@ -235,7 +422,7 @@ template <class B, int P> HGF_D Dual<B, P> x_exp(const Dual<B, P>& a) {
 template <class B, int P> HGF_D Dual<B, P> x_log(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_log(a.v);
   if constexpr (P > 0) {
-    const B inv = b_rcp(a.v);
+    const B inv = t_rcp(a.v);
 #pragma unroll
     for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
   }
@@ -266,12 +453,12 @@ template <class B, int P> HGF_D Dual<B, P> x_erf(const Dual<B, P>& a) {
   for (int i = 0; i < P; ++i) r.d[i] = c * a.d[i];
   return r;
 }
-template <class B, int P> HGF_D Dual<B, P> x_pow(const Dual<B, P>& a, const Dual<B, P>& b) {
-  // jnp.power JVP: y x^(y-1) dx + log(x) x^y dy
-  Dual<B, P> r; r.v = b_pow(a.v, b.v);
+// jnp.power JVP given the primal r = x^y: y x^(y-1) dx + log(x) x^y dy
+template <class B, int P> HGF_D Dual<B, P> pow_with_primal(B primal, const Dual<B, P>& a, const Dual<B, P>& b) {
+  Dual<B, P> r; r.v = primal;
   if constexpr (P > 0) {
-#ifdef HGF_SFU_MATH
-    const B da = b.v * r.v * b_rcp(a.v);
+#ifdef HGF_SFU_TANGENTS
+    const B da = b.v * r.v * t_rcp(a.v);
 #else
     const B da = b.v * b_pow(a.v, b.v - B(1));
 #endif
@@ -285,6 +472,12 @@ template <class B, int P> HGF_D Dual<B, P> x_pow(const Dual<B, P>& a, const Dual
   }
   return r;
 }
+template <class B, int P> HGF_D Dual<B, P> x_pow(const Dual<B, P>& a, const Dual<B, P>& b) {
+  return pow_with_primal(b_pow(a.v, b.v), a, b);
+}
+// libm / libdevice pow whatever the policy (<= 1 ulp in practice): see the inverse-temperature response
+HGF_D float exact_pow(float x, float y) { return ::powf(x, y); }
+HGF_D double exact_pow(double x, double y) { return ::pow(x, y); }
 
 // jnp.where: the derivative follows the selected branch.
 template <class T> HGF_D T x_where(bool c, const T& a, const T& b) { return c ? a : b; }
@@ -305,16 +498,25 @@ template <class T> HGF_D bool x_isfinite(const T& a) { return b_isfinite(pv(a));
 template <class T> HGF_D bool x_isnan(const T& a) { return b_isnan(pv(a)); }
 
 // jax.nn.sigmoid == lax.logistic == 1 / (1 + exp(-x))
-HGF_D float x_sigmoid(float x) { return b_div(1.0f, 1.0f + b_exp(-x)); }
+HGF_D float x_sigmoid(float x) { return b_rcp(1.0f + b_exp(-x)); }
 HGF_D double x_sigmoid(double x) { return 1.0 / (1.0 + b_exp(-x)); }
 template <class B, int P> HGF_D Dual<B, P> x_sigmoid(const Dual<B, P>& x) {
   // primal exactly as above; tangent in closed form, s (1 - s) dx, instead of differentiating exp and the division
   Dual<B, P> r;
-#ifdef HGF_SFU_MATH
   r.v = b_rcp(B(1) + b_exp(-x.v));
-#else
-  r.v = b_div(B(1), B(1) + b_exp(-x.v));
-#endif
+  if constexpr (P > 0) {
+    const B c = r.v * (B(1) - r.v);
+#pragma unroll
+    for (int i = 0; i < P; ++i) r.d[i] = c * x.d[i];
+  }
+  return r;
+}
+
+// The same with the reciprocal at IEEE accuracy: for a sigmoid whose complement 1 - s is taken when s is next to 1
+// (the binary node's prediction: 1 - mu_hat feeds its surprise), where one ulp of s is per cents of 1 - s.
+template <class B, int P> HGF_D Dual<B, P> x_sigmoid_exact(const Dual<B, P>& x) {
+  Dual<B, P> r;
+  r.v = exact_rcp(B(1) + b_exp(-x.v));
   if constexpr (P > 0) {
     const B c = r.v * (B(1) - r.v);
 #pragma unroll
@@ -340,7 +542,7 @@ template <class B, int P> HGF_D Dual<B, P> x_logaddexp(const Dual<B, P>& a, cons
     // the weights exp(x1 - out), exp(x2 - out) sum to one: w(larger) = 1 / (1 + exp(-|x1 - x2|)), w(smaller) = 1 - it
     // (one reciprocal instead of two exponentials); a NaN anywhere gives NaN weights, as the JVP's would be
     const B e = b_exp(-b_abs(a.v - b.v));
-    const B w_hi = b_rcp(B(1) + e), w_lo = B(1) - w_hi;
+    const B w_hi = t_rcp(B(1) + e), w_lo = B(1) - w_hi;
     const bool a_hi = a.v >= b.v;
     const B wa = a_hi ? w_hi : w_lo, wb = a_hi ? w_lo : w_hi;
 #pragma unroll
@@ -368,7 +570,7 @@ template <class B, int P> HGF_D Dual<B, P> x_lambert_w0(const Dual<B, P>& z) {
   // custom JVP, pyhgf/math.py:491-498: z_dot / (exp(w) (1 + w))
   Dual<B, P> r; r.v = b_lambert_w0<B>(z.v);
   if constexpr (P > 0) {
-    const B inv = b_rcp(b_exp(r.v) * (B(1) + r.v));
+    const B inv = t_rcp(b_exp(r.v) * (B(1) + r.v));
 #pragma unroll
     for (int i = 0; i < P; ++i) r.d[i] = z.d[i] * inv;
   }

@@ -122,7 +122,11 @@ template <class T, class A> HGF_D void predict_binary(const A& a, T* s, int node
   T mu = T(B(0));
 #pragma unroll (A::kUnroll)
   for (int k = 0; k < a.n_vp(node); ++k) mu = mu + HGF_S(a.vp(node, k), F_EXPECTED_MEAN);
+#if HGF_RESP_MODE != 0
+  mu = x_sigmoid_exact(mu);
+#else
   mu = x_sigmoid(mu);
+#endif
   const T c = s[a.slot_clip()];
   mu = x_clip(mu, c, B(1) - c);
   HGF_S(node, F_EXPECTED_MEAN) = mu;
@@ -676,9 +680,37 @@ HGF_D TR response_step(const A& a, const T* s, const TR* rp, int response_fn, ba
     case RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE: {  // response.py:167-215
       const TR mu = HGF_R(0, F_EXPECTED_MEAN);
       const TR temp = rp[0];
+      const bool decided_one = resp_input != B(0);
+#if HGF_RESP_MODE == 0
       const TR p1 = x_pow(mu, temp);
       const TR p0 = x_pow(B(1) - mu, temp);
-      return nan_to_inf(binary_surprise(resp_input != B(0), p1 / (p1 + p0)));
+      return nan_to_inf(binary_surprise(decided_one, p1 / (p1 + p0)));
+#else
+      // The surprise of a decision 0 is -log(1 - p): next to p = 1 (a saturated belief contradicted by the decision)
+      // ONE ulp of p is per cents of 1 - p, and a belief pinned at the clipping value repeats the same rounding at
+      // every such trial.  Matching the reference there takes its arithmetic to the last bit: libm-grade pow and an
+      // IEEE quotient (HGF_RESP_MODE 1: always; 2: only when a lane of the warp is in that regime -- the branch is
+      // warp-uniform), while everywhere else the SFU pow's 1e-6 relative error moves the surprise by 1e-6.
+      const TR one_minus_mu = B(1) - mu;
+      B v1, v0;
+#if HGF_RESP_MODE == 2 && defined(__CUDA_ARCH__)
+      bool exact = true;
+      if constexpr (sizeof(B) == 4) {
+        v1 = b_pow(pv(mu), pv(temp));
+        v0 = b_pow(pv(one_minus_mu), pv(temp));
+        const B p_fast = v1 * sfu_rcp(v1 + v0);
+        exact = __any_sync(0xffffffffu, !decided_one && !(p_fast < B(0.96875)));
+      }
+      if (exact)
+#endif
+      {
+        v1 = exact_pow(pv(mu), pv(temp));
+        v0 = exact_pow(pv(one_minus_mu), pv(temp));
+      }
+      const TR p1 = pow_with_primal(v1, mu, temp);
+      const TR p0 = pow_with_primal(v0, one_minus_mu, temp);
+      return nan_to_inf(binary_surprise(decided_one, exact_div(p1, p1 + p0)));
+#endif
     }
     default: return TR(B(0));
   }

@@ -36,37 +36,44 @@ def _variant_bit(pf: int, pr: int) -> int:
     return 1 << (pf + 5 * pr)
 
 
-def header_for(network) -> tuple:
-    """(name, header text) of the network's topology accessor; the name is a content hash."""
+def header_for(network, salt: str = "") -> tuple:
+    """(name, header text) of the network's topology accessor; the name is a content hash (salted with any extra
+    compiler flags, so that differently-built kernels of one topology never share a symbol name)."""
     inputs = network.input_idxs
     body = codegen.generate_header("@", network, network.volatility_updates, network.mean_field_updates, inputs=inputs)
-    name = "h" + hashlib.sha1(body.encode()).hexdigest()[:14]
+    name = "h" + hashlib.sha1((body + salt).encode()).hexdigest()[:14]
     return name, body.replace("Topo_@", "Topo_" + name).replace('"@"', f'"{name}"')
 
 
 def specialise(network, float32: Iterable[Sequence[int]] = ((0, 0),), float64: Iterable[Sequence[int]] = (),
-               verbose: bool = False) -> str:
+               verbose: bool = False, extra_flags: Sequence[str] = (), load: bool = True) -> str:
     """Build (or load from the cache) and register the specialisation of ``network``'s topology.
 
     float32 / float64 : the kernels to instantiate, as ``(PF, PR)`` pairs -- PF filter-parameter tangent
         directions (0 = the plain filter, up to 4 per pass), PR = 1 adds a response-parameter tangent.
         A launch that needs a kernel that was not instantiated runs through the interpreter.
+    extra_flags : further nvcc flags for the kernel translation units (e.g. a math policy, ``-DHGF_EXP_MODE=2``:
+        tools/parity_ablation.py builds one object per policy this way).
+    load : False only builds the object (no GPU or loaded library needed: the CPU box pre-builds what the GPU box runs).
     Returns the kernel name the network's plans will report (``"specialised:<hash>"``).
     """
-    L = _lib.lib()
-    name, header = header_for(network)
+    extra_flags = [str(f) for f in extra_flags]
+    name, header = header_for(network, salt=" ".join(extra_flags))
     f32 = sorted({(int(a), int(b)) for a, b in float32})
     f64 = sorted({(int(a), int(b)) for a, b in float64})
     for pf, pr in f32 + f64:
         if not (0 <= pf <= 4 and pr in (0, 1)):
             raise ValueError("kernels are (PF, PR) with 0 <= PF <= 4 and PR in (0, 1)")
     # content tag: kernels, math policy, every source the objects are compiled from (no paths: the cache travels)
-    tag = hashlib.sha1(repr((f32, f64, build.MATH, _source_hash(), header)).encode()).hexdigest()[:12]
+    tag = hashlib.sha1(repr((f32, f64, build.MATH, _source_hash(), header, extra_flags)).encode()).hexdigest()[:12]
     so = os.path.join(OUT_DIR, f"libhgf_{name}_{tag}.so")
     label = f"specialised:{name}"
+    if not os.path.exists(so):
+        _compile(name, header, f32, f64, so, label, verbose, extra_flags)
+    if not load:
+        return label
+    L = _lib.lib()
     if _registered.get(name) != so:
-        if not os.path.exists(so):
-            _compile(name, header, f32, f64, so, label, verbose)
         _lib.check(L.hgf_register_specialisation(so.encode()))
         _registered[name] = so
     if hasattr(network, "_invalidate_plan"):
@@ -81,7 +88,7 @@ def _source_hash() -> str:
     return h.hexdigest()
 
 
-def _compile(name, header, f32, f64, so, label, verbose):
+def _compile(name, header, f32, f64, so, label, verbose, extra_flags=()):
     work = os.path.join(WORK_DIR, name)
     os.makedirs(work, exist_ok=True)
     os.makedirs(OUT_DIR, exist_ok=True)
@@ -92,7 +99,7 @@ def _compile(name, header, f32, f64, so, label, verbose):
     for base, kernels in (("float", f32), ("double", f64)):
         for pf, pr in kernels:
             jobs.append((os.path.join(build.CSRC, "hgf_static_inst.cu"), os.path.join(work, f"inst_{base}_d{pf}r{pr}.o"),
-                         topo_flags + [f"-DHGF_BASE={base}", f"-DHGF_NTAN={pf}", f"-DHGF_NRESP={pr}"]))
+                         topo_flags + [f"-DHGF_BASE={base}", f"-DHGF_NTAN={pf}", f"-DHGF_NRESP={pr}"] + list(extra_flags)))
     m32 = sum(_variant_bit(pf, pr) for pf, pr in f32)
     m64 = sum(_variant_bit(pf, pr) for pf, pr in f64)
     jobs.append((os.path.join(build.CSRC, "hgf_specialisation.cu"), os.path.join(work, "table.o"),

@@ -14,6 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "..", ".."))
 sys.path.insert(0, os.path.join(HERE, ".."))
 import nets  # noqa: E402
+from oracle import conditioning  # noqa: E402
 from oracle import network as onet  # noqa: E402
 
 d = np.load(os.path.join(HERE, "..", "..", "pyhgf_b200", "data", "datasets.npz"))
@@ -39,13 +40,29 @@ o32 = nets.binary3(onet.Network).create_belief_propagation_fn()
 s32 = o32.batch_surprise(u, slots, p, "binary_softmax_inverse_temperature", resp_inputs=y)
 out["config4/params"], out["config4/surprise"], out["config4/gradient"], out["config4/surprise_f32"] = p, s, g, s32
 
+
+# the float32 oracle's gradients (Dual<float>) and, per instance, how far its own float32 results move when the filter
+# parameters move by 1e-6 relative (oracle/conditioning.py): the bound the float32 launches are held to
+def _f32(q):
+    s_, g_ = o32.batch_grad(u, slots, q, "binary_softmax_inverse_temperature", resp_inputs=y, dtype=32)
+    return np.concatenate([s_[None], g_])
+
+
+g32 = _f32(p)[1:]
+floor = np.concatenate([[0.0], 1e-4 * np.abs(g32).max(axis=1)])[:, None]
+base, sens = conditioning.sensitivity(_f32, p, rows=[0, 1], n_draws=16, floor=floor)
+assert np.array_equal(base[0], s32)
+out["config4/gradient_f32"], out["config4/sensitivity_f32"] = g32, sens
+
 # config 2: first-level Gaussian surprise of the 4-node continuous HGF
 pc = np.stack([np.clip(rng.normal(m, 1.0, n), m - 2, m + 2) for m in (-13.0, -2.0, -2.0)]).astype(np.float32).astype(np.float64)
 oc = nets.continuous3(onet.Network, dtype="float64").create_belief_propagation_fn()
 slots_c = [oc.slot(i, "tonic_volatility") for i in (1, 2, 3)]
 out["config2/params"] = pc
 out["config2/surprise"] = oc.batch_surprise(x, slots_c, pc, "first_level_gaussian_surprise")
-out["config2/surprise_f32"] = nets.continuous3(onet.Network).create_belief_propagation_fn().batch_surprise(x, slots_c, pc, "first_level_gaussian_surprise")
+oc32 = nets.continuous3(onet.Network).create_belief_propagation_fn()
+out["config2/surprise_f32"], out["config2/sensitivity_f32"] = conditioning.sensitivity(
+    lambda q: oc32.batch_surprise(x, slots_c, q, "first_level_gaussian_surprise"), pc, n_draws=16, floor=100.0)
 
 path = os.path.join(HERE, "oracle_vectors.npz")
 np.savez_compressed(path, **out)

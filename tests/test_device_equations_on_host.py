@@ -1,0 +1,58 @@
+"""The DEVICE update equations (pyhgf_b200/csrc/hgf_math.cuh, hgf_ops.cuh, hgf_scan.cuh are __host__ __device__)
+compiled for the host by tools/hostsim and run against the oracle -- the CUDA source itself is tied to the oracle on a
+machine without a GPU:
+
+  * with IEEE / libm primitives the kernel's time loop reproduces the float32 oracle's summed surprise BIT FOR BIT
+    (same equations, same operation order), and its forward-mode tangents give the oracle's gradients;
+  * with the SFU primitives emulated inside their documented error bounds and the SHIPPED math policy, every instance
+    stays inside the parity bound the GPU tests assert (tests/parity.py); with the response's last-bit arithmetic
+    switched off (round 1's policy) it does not.
+"""
+
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools", "hostsim"))
+
+import nets  # noqa: E402
+from oracle import conditioning  # noqa: E402
+from oracle import network as onet  # noqa: E402
+from parity import assert_conditioned  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def box(datasets):
+    import run as hostsim
+
+    rng = np.random.default_rng(7)
+    n = 1024
+    p = np.stack([rng.uniform(-6, -3, n), rng.uniform(-6, -3, n), np.exp(rng.uniform(-0.3, 0.8, n))])
+    return hostsim, hostsim.Box("box", datasets["u"], datasets["y"], p, 0)
+
+
+def test_ieee_build_of_the_device_equations_is_the_oracle(box):
+    hostsim, b = box
+    logp, grad = b.run(hostsim.build(["@"]))
+    assert np.array_equal(logp.astype(np.float32), b.want.astype(np.float32))  # bit for bit
+    for i in range(3):  # the kernel's closed-form JVPs against the oracle's operation-by-operation Dual<float>
+        scale = np.abs(b.want_g[i]).max()
+        rel = np.abs(grad[i] - b.want_g[i]) / (np.abs(b.want_g[i]) + 1e-4 * scale)
+        assert np.median(rel) < 1e-6 and np.quantile(rel, 0.99) < 1e-3, (i, float(np.median(rel)), float(rel.max()))
+
+
+def test_shipped_policy_with_emulated_sfu_stays_inside_the_parity_bound(box):
+    hostsim, b = box
+    o32 = nets.binary3(onet.Network).create_belief_propagation_fn()
+    slots = [o32.slot(1, "tonic_volatility"), o32.slot(2, "tonic_volatility"), o32.slot(-1, "response_parameter", 0)]
+    want, sens = conditioning.sensitivity(
+        lambda q: o32.batch_surprise(b.u.astype(np.float64), slots, q, "binary_softmax_inverse_temperature", resp_inputs=b.y.astype(np.float64)),
+        b.p.astype(np.float64), rows=[0, 1], n_draws=16)
+    shipped, _ = b.run(hostsim.build([]))  # the defaults of hgf_math.cuh
+    stats = assert_conditioned(shipped, want, sens, 1e-4, what="shipped policy, emulated SFU", max_relaxed=0.02)
+    round1, _ = b.run(hostsim.build(["-DHGF_RESP_MODE=0"]))
+    err = np.abs(round1 / want - 1)
+    assert (err > conditioning.tolerance(sens, 1e-4, 4.0)).sum() > stats["n_over_rtol"] + 2  # what the policy fixes

@@ -1,9 +1,10 @@
 """Parity of the CUDA path (through the C ABI) with the CPU oracle and with the reference's goldens.
 
 Tolerances (BASELINE.json north_star): float32, <= 1e-5 relative on per-trial means and precisions,
-<= 1e-4 relative on summed surprise / logp and on gradients (well-conditioned parameter sets; the
-saturating regimes of SURVEY.md §4 are finite/order-of-magnitude checks).  float64 launches are held to
-1e-9.  Everything here needs a B200: run with ``-m gpu``.
+<= 1e-4 relative on summed surprise / logp and on gradients, asserted on EVERY instance of every batch: where the
+oracle's own float32 result moves by more than the tolerance under a 1e-6 relative change of its parameters
+(oracle/conditioning.py) the instance's bound is a small multiple of that sensitivity instead (tests/parity.py).
+float64 launches are held to 1e-9.  Everything here needs a B200: run with ``-m gpu``.
 """
 
 import ctypes as C
@@ -12,7 +13,9 @@ import numpy as np
 import pytest
 
 import nets
+from oracle import conditioning
 from oracle import network as onet
+from parity import AMPLIFICATION_GRAD, assert_conditioned
 
 pytestmark = pytest.mark.gpu
 
@@ -41,25 +44,42 @@ def R():
     return response
 
 
-def assert_traj_close(gnet, onet_, nodes, rtol, atol=1e-7, keys=nets.BELIEFS):
+def assert_traj_close(gnet, onet_, nodes, rtol, atol=1e-7, keys=nets.BELIEFS, sens=None):
+    """Every recorded belief at every trial; `sens` (traj_sensitivity): the oracle's own reproducibility of each value."""
     for node in nodes:
         for k in keys:
             a = np.asarray(gnet.node_trajectories[node][k], dtype=np.float64)
             b = np.asarray(onet_.node_trajectories[node][k], dtype=np.float64)
             assert a.shape == b.shape
             assert np.array_equal(np.isnan(a), np.isnan(b)), (node, k)
-            ok = np.isclose(a, b, rtol=rtol, atol=atol, equal_nan=True)
+            tol = rtol if sens is None else conditioning.tolerance(sens[(node, k)], rtol, 4.0)
+            with np.errstate(invalid="ignore"):
+                ok = (np.abs(a - b) <= atol + tol * np.abs(b)) | (np.isnan(a) & np.isnan(b)) | (a == b)
             assert ok.all(), (node, k, float(np.nanmax(np.abs(a - b) / (np.abs(b) + atol))))
 
 
-def assert_mostly_close(got, want, rtol, atol=0.0, frac=0.98, what=""):
-    """Wide parameter boxes contain rounding-sensitive instances (runaway beliefs, branch flips of the
-    where/clip guards: SURVEY.md §4): there the float32 CUDA and float32 CPU trajectories legitimately
-    diverge.  Hold the stated tolerance on at least `frac` of the instances and the non-finite pattern on all."""
-    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
-    assert np.array_equal(np.isfinite(got), np.isfinite(want)), what
-    ok = np.isclose(got, want, rtol=rtol, atol=atol, equal_nan=True)
-    assert ok.mean() >= frac, (what, float(ok.mean()))
+def traj_sensitivity(run_oracle, nodes, keys=nets.BELIEFS, eps=1e-6, n_draws=4, seed=5):
+    """`run_oracle(perturb)` builds the oracle network, calls `perturb(net)` on it before the data are fed, runs it and
+    returns it.  Per recorded value: the largest relative change over a few runs whose tonic volatilities moved by
+    `eps` relative -- how reproducible the float32 oracle's own trajectory is (oracle/conditioning.py)."""
+    base = run_oracle(lambda net: None)
+    rng = np.random.default_rng(seed)
+    sens = {(n, k): np.zeros(np.shape(base.node_trajectories[n][k])) for n in nodes for k in keys}
+
+    def perturb(net):
+        for node, attrs in net.attributes.items():
+            if isinstance(node, int) and node >= 0 and "tonic_volatility" in attrs:
+                attrs["tonic_volatility"] = float(attrs["tonic_volatility"]) * (1.0 + eps * rng.uniform(-1, 1))
+
+    for _ in range(n_draws):
+        other = run_oracle(perturb)
+        for key in sens:
+            b = np.asarray(base.node_trajectories[key[0]][key[1]], dtype=np.float64)
+            c = np.asarray(other.node_trajectories[key[0]][key[1]], dtype=np.float64)
+            with np.errstate(invalid="ignore", divide="ignore"):
+                d = np.abs(c - b) / (np.abs(b) + 1e-7)
+            sens[key] = np.maximum(sens[key], np.nan_to_num(d, nan=0.0, posinf=0.0))
+    return sens
 
 
 # ------------------------------------------------------------------ reference goldens, straight on the GPU
@@ -224,24 +244,22 @@ def test_batched_binary_logp_matches_oracle(G, R, datasets, n):
                   last_attributes=True, record=[(1, "mean"), (2, "precision")])
     o = nets.binary3(onet.Network).create_belief_propagation_fn()
     slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
-    want, last = o.batch_surprise(u, slots, np.stack([om2, om3, temp]), "binary_softmax_inverse_temperature",
-                                  resp_inputs=y, return_last=True)
+
+    def oracle(p):  # summed surprise and the two recorded beliefs at the last trial, [3][n]
+        s_, last = o.batch_surprise(u, slots, p, "binary_softmax_inverse_temperature", resp_inputs=y, return_last=True)
+        return np.stack([s_, last[:, o.slot(1, "mean")], last[:, o.slot(2, "precision")]])
+
+    p = np.stack([om2, om3, temp]).astype(np.float32).astype(np.float64)
+    (want, m1, p2), sens = conditioning.sensitivity(oracle, p, rows=[0, 1], floor=1e-6)
     got = res.surprise.double().cpu().numpy()
     assert tuple(res.pointwise.shape) == (n, 320)
-    # the box reaches omega = -2.5, where the second-level belief starts to run away (SURVEY §4's
-    # rounding-sensitive regime); the stated tolerances are asserted on every well-conditioned instance
-    # (omega <= -3.5) and on most of the box
-    m1, p2 = last[:, o.slot(1, "mean")], last[:, o.slot(2, "precision")]
-    calm = (np.abs(m1) < 50.0) & (om2 < -3.5) & (om3 < -3.5)
-    assert calm.sum() >= n // 4
-    assert np.allclose(got[calm], want[calm], rtol=RTOL_SUM)
-    assert_mostly_close(got, want, RTOL_SUM, frac=0.9, what="surprise")
-    assert_mostly_close(res.pointwise.sum(1).double().cpu().numpy(), want, RTOL_SUM, frac=0.9, what="pointwise")
-    for got_t, want_v in [(res.last_attributes[(1, "mean")], m1), (res.trajectories[(1, "mean")][:, -1], m1),
-                          (res.trajectories[(2, "precision")][:, -1], p2)]:
-        got_v = got_t.double().cpu().numpy()
-        assert np.allclose(got_v[calm], want_v[calm], rtol=RTOL_TRAJ, atol=1e-6)
-        assert_mostly_close(got_v, want_v, RTOL_TRAJ, atol=1e-6, frac=0.8)
+    # the box reaches omega = -2.5, where the second-level belief starts to run away: every instance is
+    # held to the stated tolerance or, where the oracle itself is not reproducible to it, to its own sensitivity
+    assert_conditioned(got, want, sens[0], RTOL_SUM, what="surprise")
+    assert_conditioned(res.pointwise.sum(1).double().cpu().numpy(), want, sens[0], RTOL_SUM, what="pointwise")
+    for got_t, want_v, sn in [(res.last_attributes[(1, "mean")], m1, sens[1]), (res.trajectories[(1, "mean")][:, -1], m1, sens[1]),
+                              (res.trajectories[(2, "precision")][:, -1], p2, sens[2])]:
+        assert_conditioned(got_t.double().cpu().numpy(), want_v, sn, RTOL_TRAJ, floor=1e-6, what="last beliefs")
 
 
 def test_batched_continuous_logp_matches_oracle(G, R, datasets):
@@ -281,27 +299,38 @@ def test_gradient_matches_dual_oracle(G, R, datasets, dtype, rtol):
         p = p.astype(np.float32).astype(np.float64)
     # like-for-like precision: the float32 kernel is checked against the Dual<float> oracle (north_star: <= 1e-4
     # relative on summed logp and gradients), the float64 kernel against Dual<double>
-    want_s, want_g = o.batch_grad(u, slots, p, "binary_softmax_inverse_temperature", resp_inputs=y,
-                                  dtype=32 if dtype == "float32" else 64)
-    assert np.allclose(res.surprise.double().cpu().numpy(), want_s, rtol=rtol)
-    for i, k in enumerate(keys):
-        got = res.gradient[k].double().cpu().numpy()
-        scale = np.abs(want_g[i]).max()
-        if dtype == "float64":
-            assert np.allclose(got, want_g[i], rtol=rtol, atol=rtol * scale), (k, np.abs(got - want_g[i]).max(), scale)
-        else:
-            # float32 derivatives through 320 recursive steps amplify the ulp-level exp/log differences between
-            # CUDA and glibc: per instance the bound carries an absolute term (1e-3 of the largest gradient) ...
-            assert np.allclose(got, want_g[i], rtol=rtol, atol=1e-3 * scale), (k, np.abs(got - want_g[i]).max(), scale)
-            assert_mostly_close(got, want_g[i], rtol, atol=rtol * scale, frac=0.95, what=k)
-        # ... and the gradient summed over instances (what a sampler's all-reduce carries) is held to the stated 1e-4
-        assert np.isclose(got.sum(), want_g[i].sum(), rtol=rtol * (1 if dtype == "float64" else 3), atol=rtol * np.abs(want_g[i]).sum() / n ** 0.5), (k, got.sum(), want_g[i].sum())
-    if dtype == "float32":  # and the float32 gradient is a faithful gradient: close to the float64 one
-        _, g64 = o.batch_grad(u, slots, p, "binary_softmax_inverse_temperature", resp_inputs=y)
+
+    def oracle(q):
+        s_, g_ = o.batch_grad(u, slots, q, "binary_softmax_inverse_temperature", resp_inputs=y, dtype=32 if dtype == "float32" else 64)
+        return np.concatenate([s_[None], g_])
+
+    if dtype == "float64":
+        want = oracle(p)
+        want_s, want_g = want[0], want[1:]
+        assert np.allclose(res.surprise.double().cpu().numpy(), want_s, rtol=rtol)
         for i, k in enumerate(keys):
             got = res.gradient[k].double().cpu().numpy()
-            rel = np.abs(got - g64[i]) / (np.abs(g64[i]) + 1e-3 * np.abs(g64[i]).max())
-            assert np.median(rel) < 1e-4, (k, np.median(rel))
+            scale = np.abs(want_g[i]).max()
+            assert np.allclose(got, want_g[i], rtol=rtol, atol=rtol * scale), (k, np.abs(got - want_g[i]).max(), scale)
+        return
+    # float32: every instance, logp and every gradient, to the stated 1e-4 (a gradient that crosses zero is measured
+    # against |g| + 1e-4 max|g|) or to the oracle's own reproducibility where that is worse
+    scales = np.abs(oracle(p)[1:]).max(axis=1)
+    floor = np.concatenate([[0.0], rtol * scales])[:, None]
+    want, sens = conditioning.sensitivity(oracle, p, rows=[0, 1, 3, 4], n_draws=16, floor=floor)
+    want_s, want_g = want[0], want[1:]
+    assert_conditioned(res.surprise.double().cpu().numpy(), want_s, sens[0], rtol, what="logp", max_relaxed=0.02)
+    for i, k in enumerate(keys):
+        got = res.gradient[k].double().cpu().numpy()
+        assert_conditioned(got, want_g[i], sens[1 + i], rtol, amplification=AMPLIFICATION_GRAD, floor=rtol * scales[i], what=k)
+        # the gradient summed over instances (what a sampler's all-reduce carries) is held to the stated 1e-4 as well
+        assert np.isclose(got.sum(), want_g[i].sum(), rtol=3 * rtol, atol=rtol * np.abs(want_g[i]).sum() / n ** 0.5), (k, got.sum(), want_g[i].sum())
+    # and the float32 gradient is a faithful gradient: close to the float64 one
+    _, g64 = o.batch_grad(u, slots, p, "binary_softmax_inverse_temperature", resp_inputs=y)
+    for i, k in enumerate(keys):
+        got = res.gradient[k].double().cpu().numpy()
+        rel = np.abs(got - g64[i]) / (np.abs(g64[i]) + 1e-3 * np.abs(g64[i]).max())
+        assert np.median(rel) < 1e-4, (k, np.median(rel))
 
 
 def test_gradient_continuous_and_coupling(G, R, datasets):
@@ -437,15 +466,17 @@ def test_config3_grid_properties(G, R, datasets):
     assert torch.equal(torch.nan_to_num(a[perm], nan=-1.0), torch.nan_to_num(c, nan=-1.0))
     idx = np.random.default_rng(0).choice(side * side, 512, replace=False)
     o = nets.binary3(onet.Network).create_belief_propagation_fn()
-    want = o.batch_surprise(u, [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility")],
-                            np.stack([om2[idx], om3[idx]]).astype(np.float32).astype(np.float64), "first_level_binary_surprise")
+    oslots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility")]
+    ps = np.stack([om2[idx], om3[idx]]).astype(np.float32).astype(np.float64)
+    want, sens = conditioning.sensitivity(lambda q: o.batch_surprise(u, oslots, q, "first_level_binary_surprise"), ps)
     got = a[torch.as_tensor(idx, device="cuda")].double().cpu().numpy()
     finite = np.isfinite(want)
     assert np.array_equal(finite, np.isfinite(got))
-    # the grid reaches omega = 0 (saturating, rounding-sensitive: SURVEY §4): hold the well-conditioned part to 1e-4
-    calm = finite & (om2[idx] < -2.0) & (om3[idx] < -2.0)
+    # the grid reaches omega = 0: beyond omega = -2.5 the beliefs saturate and float32 itself is not reproducible
+    # (reference tests/test_model.py:237-268 documents that regime); everything below it is held to 1e-4 per instance
+    calm = finite & (om2[idx] <= -2.5) & (om3[idx] <= -2.5)
     assert calm.sum() > 100
-    assert np.allclose(got[calm], want[calm], rtol=RTOL_SUM)
+    assert_conditioned(got[calm], want[calm], sens[calm], RTOL_SUM, what="config3 sample", max_relaxed=0.05)
     rel = np.abs(got[finite] - want[finite]) / np.abs(want[finite])
     assert np.median(rel) < 1e-5
 
@@ -580,29 +611,36 @@ def test_config4_full_size_properties(G, R):
     assert torch.equal(sub.surprise, logp[lo * n_chain:(lo + 2) * n_chain])           # (ii)
     for k in keys:
         assert torch.equal(sub.gradient[k], res.gradient[k][lo * n_chain:(lo + 2) * n_chain])
+    # (iii) every gradient is the derivative of logp: central differences in float64, all three parameters
     sel = slice(lo * n_chain, lo * n_chain + 32)
     p64 = p[:, sel].astype(np.float64)
-    h = 1e-6
-    up, dn = p64.copy(), p64.copy()
-    up[2] += h
-    dn[2] -= h
     u1, y1 = u[lo:lo + 1], y[lo:lo + 1]
     f = lambda q: run(u1, y1, q, dtype="float64").surprise.cpu().numpy()  # noqa: E731
-    fd = (f(up) - f(dn)) / (2 * h)
-    g64 = run(u1, y1, p64, dtype="float64").gradient[keys[2]].cpu().numpy()
-    assert np.allclose(g64, fd, rtol=1e-5, atol=1e-6)                                  # (iii)
-    g32 = res.gradient[keys[2]][sel].double().cpu().numpy()
-    assert np.median(np.abs(g32 - g64) / (np.abs(g64) + 1e-3 * np.abs(g64).max())) < 1e-4
-    idx = np.random.default_rng(3).choice(n, 256, replace=False)                      # (iv)
+    r64 = run(u1, y1, p64, dtype="float64")
+    for j, k in enumerate(keys):
+        h = 1e-6
+        up, dn = p64.copy(), p64.copy()
+        up[j] += h
+        dn[j] -= h
+        fd = (f(up) - f(dn)) / (2 * h)
+        g64 = r64.gradient[k].cpu().numpy()
+        assert np.allclose(g64, fd, rtol=2e-5, atol=2e-5 * np.abs(fd).max()), (k, np.abs(g64 - fd).max())
+        g32 = res.gradient[k][sel].double().cpu().numpy()
+        assert np.median(np.abs(g32 - g64) / (np.abs(g64) + 1e-3 * np.abs(g64).max())) < 1e-4, k
+    # (iv) a random sample against the oracle, every sampled instance
+    idx = np.sort(np.random.default_rng(3).choice(n, 256, replace=False))
     o = nets.binary3(onet.Network).create_belief_propagation_fn()
-    o64 = nets.binary3(onet.Network, dtype="float64").create_belief_propagation_fn()
     slots = [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility"), o.slot(-1, "response_parameter", 0)]
     got = -logp[torch.as_tensor(idx, device="cuda")].double().cpu().numpy()
-    s32 = np.array([o.batch_surprise(u[i // n_chain], slots, p[:, [i]].astype(np.float64), "binary_softmax_inverse_temperature", resp_inputs=y[i // n_chain])[0] for i in idx])
-    s64 = np.array([o64.batch_surprise(u[i // n_chain], slots, p[:, [i]].astype(np.float64), "binary_softmax_inverse_temperature", resp_inputs=y[i // n_chain])[0] for i in idx])
-    well = np.abs(s32 / s64 - 1) <= 1e-5
-    assert well.mean() > 0.8
-    assert np.allclose(got[well], s32[well], rtol=RTOL_SUM)
+
+    def oracle(q):  # instance i of the sample reads participant idx[i] // n_chain's series
+        return np.array([o.batch_surprise(u[i // n_chain], slots, q[:, [c]], "binary_softmax_inverse_temperature", resp_inputs=y[i // n_chain])[0]
+                         for c, i in enumerate(idx)])
+
+    want, sens = conditioning.sensitivity(oracle, p[:, idx].astype(np.float64), rows=[0, 1])
+    # config 4's chains spread over omega in [-8, -1]: the saturating part of that box is not reproducible in
+    # float32 (the bound follows the oracle's own sensitivity there); no instance is dropped
+    assert_conditioned(got, want, sens, RTOL_SUM, what="config4 sample")
 
 
 def test_config2_full_size_properties(G, R, datasets):
@@ -805,11 +843,13 @@ def test_committed_golden_vectors(G, R, datasets):
             for i, k in enumerate(keys):
                 assert np.allclose(res.gradient[k].cpu().numpy(), v["config4/gradient"][i], rtol=1e-7, atol=1e-9)
         else:
-            well = np.abs(v["config4/surprise_f32"] / v["config4/surprise"] - 1) <= 1e-5
-            assert well.mean() > 0.8 and np.allclose(s[well], v["config4/surprise"][well], rtol=RTOL_SUM)
+            # float32 against the committed float32 oracle results (Dual<float> gradients), every instance, with the
+            # committed per-instance sensitivities of that oracle (tests/golden/make_oracle_vectors.py)
+            assert_conditioned(s, v["config4/surprise_f32"], v["config4/sensitivity_f32"][0], RTOL_SUM, what="config4 golden")
             for i, k in enumerate(keys):
-                gg, want = res.gradient[k].double().cpu().numpy(), v["config4/gradient"][i]
-                assert np.allclose(gg[well], want[well], rtol=1e-3, atol=1e-3 * np.abs(want).max()), k
+                gg, want = res.gradient[k].double().cpu().numpy(), v["config4/gradient_f32"][i]
+                assert_conditioned(gg, want, v["config4/sensitivity_f32"][1 + i], RTOL_SUM, amplification=AMPLIFICATION_GRAD,
+                                   floor=RTOL_SUM * np.abs(want).max(), what=k)
     keys = [(i, "tonic_volatility") for i in (1, 2, 3)]
     for dtype in ("float64", "float32"):
         res = nets.continuous3(G.Network, dtype=dtype).batch(datasets["x"], dict(zip(keys, v["config2/params"])),
@@ -820,8 +860,8 @@ def test_committed_golden_vectors(G, R, datasets):
         if dtype == "float64":
             assert np.allclose(s[fin], want[fin], rtol=1e-8, atol=1e-7)
         else:
-            well = fin & (np.abs(v["config2/surprise_f32"] - want) <= 1e-5 * (np.abs(want) + 1))
-            assert np.allclose(s[well], want[well], rtol=RTOL_SUM, atol=1e-2)
+            # the summed Gaussian surprise crosses zero (terms of magnitude ~2e3): relative to |s| + 100
+            assert_conditioned(s, v["config2/surprise_f32"], v["config2/sensitivity_f32"], RTOL_SUM, floor=100.0, what="config2 golden")
 
 
 def test_plain_c_caller_of_the_abi(G, datasets, tmp_path):
@@ -845,11 +885,9 @@ def test_plain_c_caller_of_the_abi(G, datasets, tmp_path):
     o = nets.binary3(onet.Network).create_belief_propagation_fn()
     want = o.batch_surprise(datasets["u"], [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility")], out[:, :2].T.copy(),
                             "first_level_binary_surprise")
-    o64 = nets.binary3(onet.Network, dtype="float64").create_belief_propagation_fn()
-    want64 = o64.batch_surprise(datasets["u"], [o64.slot(1, "tonic_volatility"), o64.slot(2, "tonic_volatility")], out[:, :2].T.copy(),
-                                "first_level_binary_surprise")
-    well = np.abs(want / want64 - 1) <= 1e-5
-    assert well.mean() > 0.7 and np.allclose(out[well, 2], want[well], rtol=RTOL_SUM)
+    _, sens = conditioning.sensitivity(lambda q: o.batch_surprise(datasets["u"], [o.slot(1, "tonic_volatility"), o.slot(2, "tonic_volatility")], q,
+                                                                  "first_level_binary_surprise"), out[:, :2].T.copy())
+    assert_conditioned(out[:, 2], want, sens, RTOL_SUM, what="C caller")
     # the defaults written out by hand in the C file are the front-end's: omega = -4 reproduces the reference golden
     assert np.isfinite(out[:, 2]).all()
 
@@ -1005,7 +1043,16 @@ def test_custom_sequence_matches_oracle(G, datasets, build, dtype):
     ts = rng.uniform(0.5, 2.0, len(u))
     net.input_custom_sequence(gb, idx, u, time_steps=ts)
     o.input_custom_sequence(ob, idx, u, time_steps=ts)
-    assert_traj_close(net, o, range(len(net.edges)), RTOL_TRAJ if dtype == "float32" else 1e-9)
+    sens = None
+    if dtype == "float32":  # random time steps and frozen levels: some trials amplify rounding beyond 1e-5 in the oracle itself
+
+        def run_oracle(perturb):
+            o2 = build(onet.Network, dtype=dtype).create_belief_propagation_fn()
+            perturb(o2)
+            return o2.input_custom_sequence(ob, idx, u, time_steps=ts)
+
+        sens = traj_sensitivity(run_oracle, range(len(net.edges)))
+    assert_traj_close(net, o, range(len(net.edges)), RTOL_TRAJ if dtype == "float32" else 1e-9, sens=sens)
     assert np.isclose(net.last_attributes[top]["mean"], o.last_attributes[top]["mean"], rtol=1e-5)
     # the top level really was frozen on the steps that skipped it
     frozen = np.flatnonzero(np.clip(idx, 0, 2)[1:] == 2) + 1

@@ -1,0 +1,43 @@
+// Numerics test-bed (development tool, not part of the library): the DEVICE equations of pyhgf_b200/csrc
+// (hgf_math.cuh, hgf_ops.cuh, hgf_scan.cuh -- all __host__ __device__) compiled for the HOST, so that a math
+// policy can be studied without a GPU.  With -DHGF_HOST_EMULATE_SFU the SFU primitives are emulated inside their
+// documented error bounds (hgf_math.cuh) and the policy knobs (-DHGF_DIV_MODE=..., -DHGF_RESP_MODE=...,
+// -DHGF_EXACT_DIV_SITES=...) act as they do on the device; without it every primitive is IEEE / libm.
+//   g++ -O2 -ffp-contract=off -shared -fPIC -I pyhgf_b200/csrc -I /usr/local/cuda/include [-D...] tools/hostsim/hostsim.cpp
+// See tools/hostsim/run.py.
+#include "hgf_scan.cuh"
+#include <generated/topo_binary3.h>
+#include <generated/topo_continuous3.h>
+
+using namespace hgf;
+
+template <class Topo, int PF, int PR>
+static void run(int n_inst, int n_steps, int group, const float* u, const float* y, const float* attrs, int n_params, const int* slots,
+                const float* params, int response_fn, float* logp, float* grad) {
+  Program prog{};
+  prog.max_posterior_precision = 1e10;
+  CallLists lists{};
+  lists.n_params = n_params;
+  lists.n_filter = PR ? n_params - 1 : n_params;
+  for (int q = 0; q < n_params; ++q) { lists.param_slot[q] = static_cast<uint16_t>(slots[q]); lists.param_row[q] = static_cast<uint16_t>(q); }
+  ScanArgs a{};
+  a.n_instances = n_inst; a.ld = n_inst; a.n_steps = n_steps;
+  a.input_group_size = group; a.response_group_size = group;
+  a.input_data = u; a.response_inputs = y; a.attributes = attrs; a.params = params;
+  a.surprise_sum = logp; a.gradient = (PF + PR) ? grad : nullptr;
+  a.out_scale = 1.0; a.response_fn = response_fn; a.tangent_offset = 0; a.resp_index = PR ? n_params - 1 : -1;
+#pragma omp parallel for schedule(dynamic, 64)
+  for (int i = 0; i < n_inst; ++i) scan_instance<Dual<float, PF>, Topo, Topo::kSlots, PR, true, false>(prog, lists, a, i, true);
+}
+
+extern "C" void sim_binary3_grad(int n, int T, int group, const float* u, const float* y, const float* attrs, const int* slots,
+                                 const float* params, float* logp, float* grad) {
+  run<Topo_binary3, 2, 1>(n, T, group, u, y, attrs, 3, slots, params, RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE, logp, grad);
+}
+extern "C" void sim_binary3(int n, int T, int group, const float* u, const float* y, const float* attrs, const int* slots,
+                            const float* params, int response_fn, float* logp) {
+  run<Topo_binary3, 0, 0>(n, T, group, u, y, attrs, 3, slots, params, response_fn, logp, nullptr);
+}
+extern "C" void sim_continuous3(int n, int T, const float* u, const float* attrs, const int* slots, const float* params, float* logp) {
+  run<Topo_continuous3, 0, 0>(n, T, 0, u, nullptr, attrs, 3, slots, params, RESP_FIRST_LEVEL_GAUSSIAN, logp, nullptr);
+}
