@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define HGF_ABI_VERSION 4
+#define HGF_ABI_VERSION 5
 
 /* number of scalar attribute fields per node, and their order (slot = node * HGF_N_FIELDS + field).
  * Names are the reference's attribute keys, pyhgf/model/add_nodes.py:65-85, 159-184, 330-340. */
@@ -122,10 +122,14 @@ typedef struct {
    * zero-filled before the first launch, and passes all ranks' mappings.  The kernel then sums the per-group
    * (per-chain) results of ALL ranks itself: the last block of each rank adds its G partial sums into every
    * peer's workspace over NVLink (one multimem.red per value when a multicast mapping is given, else one red per
-   * peer), signals its peers and waits for theirs -- no NCCL call follows the kernel.  When the launch completes,
-   * workspace + hgf_fused_reduce_result_offset(n_groups, dtype, epoch) holds the all-reduced [G] sums; they stay
-   * valid until the launch after next.  `reduced` must be NULL; `epoch` counts the launches on this workspace
-   * (0, 1, 2, ...) and must be the same on every rank. */
+   * peer), publishes "launch `epoch` deposited" to every peer, and the kernel ENDS -- it does not wait for the
+   * other ranks' sums, so a rank is never held back by its peers' launch skew, and no NCCL call follows the kernel.
+   * The CONSUMER waits: hgf_fused_reduce_wait(workspace, ..., epoch, stream) enqueues a one-block kernel that
+   * returns once every rank has deposited launch `epoch`; after it, workspace +
+   * hgf_fused_reduce_result_offset(n_groups, dtype, epoch) holds the all-reduced [G] sums.  They stay valid for the
+   * next HGF_FUSED_RING / 2 - 1 launches on this workspace; ranks may drift apart by as many launches (a launch
+   * that is further ahead waits for the slowest peer before depositing).  `reduced` must be NULL; `epoch` counts
+   * the launches on this workspace (0, 1, 2, ...) and must be the same on every rank. */
   int32_t n_groups;              /* G (also read by the *_host entry points: > 0 saves their scan of group[] for its maximum) */
   int32_t world_size;            /* W <= 8 */
   int32_t rank;
@@ -173,13 +177,18 @@ int hgf_filter(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
 /* Forward filter + d(surprise_sum)/d(params) in the same pass.  Device pointers. */
 int hgf_logp_grad(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
 
-/* Same, with every data pointer in HOST memory (pageable or pinned); copies in, runs, copies out, synchronises. */
+/* Same, with every data pointer in HOST memory (pageable or pinned); copies in, runs, copies out, synchronises.
+ * With a fused cross-GPU reduction (world_size > 1; peer_workspace stays a table of DEVICE addresses) a non-NULL host
+ * `reduced` receives the sums over ALL ranks: the call waits for every rank's deposit before copying them out. */
 int hgf_filter_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device);
 int hgf_logp_grad_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device);
 
-/* fused cross-GPU reduction workspace: size, and where the all-reduced [n_groups] sums of a launch are */
+/* fused cross-GPU reduction workspace: size, where the all-reduced [n_groups] sums of a launch are, and the
+ * consumer's wait for them (enqueued on `stream`; see hgf_call_t::peer_workspace) */
+#define HGF_FUSED_RING 16
 int64_t hgf_fused_reduce_bytes(int32_t n_groups, int32_t dtype);
 int64_t hgf_fused_reduce_result_offset(int32_t n_groups, int32_t dtype, uint32_t epoch);
+int hgf_fused_reduce_wait(void* workspace, int32_t n_groups, int32_t dtype, int32_t world_size, uint32_t epoch, void* stream);
 
 /* Exponential-family state node with a fixed learning rate ("generalised Bayesian filtering":
  * add_nodes(kind="ef-state", learning="generalised-filtering"), pyhgf/model/add_nodes.py:360-470;

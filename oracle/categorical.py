@@ -69,7 +69,8 @@ def categorical_update(observations, expected_mean, parent_mean, alpha0, dtype=n
             nu = pe / delta_xi - dtype(1)
             alpha = (nu * em[t] + dtype(1)).astype(dtype)
             out["kl_divergence"][t] = dirichlet_kullback_leibler(alpha_prev, alpha, dtype)
-            out["surprise"][t] = np.sum(np.where(x[t] != 0, -np.log(em[t]), -np.log(dtype(1) - em[t])), dtype=dtype)
+            emc = np.clip(em[t], dtype(1e-6), dtype(1.0 - 1e-6))  # binary_surprise(clipping=True), pyhgf/math.py:248-249
+            out["surprise"][t] = np.sum(np.where(x[t] != 0, -np.log(emc), -np.log(dtype(1) - emc)), dtype=dtype)
             out["alpha"][t] = alpha
             out["mean"][t] = updated
             alpha_prev = alpha

@@ -115,7 +115,8 @@ EXPORTS = (
     "hgf_abi_version", "hgf_last_error", "hgf_plan_create", "hgf_plan_destroy", "hgf_plan_n_slots",
     "hgf_plan_slot_coupling", "hgf_plan_slot_clipping", "hgf_plan_slot_response", "hgf_plan_kernel_name",
     "hgf_filter", "hgf_logp_grad", "hgf_filter_host", "hgf_logp_grad_host", "hgf_launch_count",
-    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_register_specialisation", "hgf_ef_filter", "hgf_categorical_update",
+    "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_fused_reduce_wait", "hgf_register_specialisation", "hgf_ef_filter",
+    "hgf_categorical_update",
 )
 
 _lib = None
@@ -210,7 +211,9 @@ def lib() -> C.CDLL:
     L.hgf_fused_reduce_bytes.restype = C.c_int64
     L.hgf_fused_reduce_result_offset.argtypes = [C.c_int32, C.c_int32, C.c_uint32]
     L.hgf_fused_reduce_result_offset.restype = C.c_int64
-    if L.hgf_abi_version() != 4:
+    L.hgf_fused_reduce_wait.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, C.c_void_p]
+    L.hgf_fused_reduce_wait.restype = C.c_int
+    if L.hgf_abi_version() != 5:
         raise ImportError("libpyhgf_cuda.so ABI version mismatch; rebuild with `python -m pyhgf_b200.build --force`")
     _lib = L
     return L

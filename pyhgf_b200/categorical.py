@@ -73,6 +73,7 @@ def update(*, bits: int, device, observations: torch.Tensor, expected_mean: torc
     c.mean = out["mean"].data_ptr() if want_vectors else None
     c.kl_divergence = out["kl_divergence"].data_ptr()
     c.surprise = out["surprise"].data_ptr()
-    s = torch.cuda.current_stream(device)  # the temporaries above are freed in this stream's order
-    _lib.check(L.hgf_categorical_update(C.byref(c), C.c_void_p(s.cuda_stream)))
+    with torch.cuda.device(device):  # the library launches on the CURRENT device: make it the tensors' one
+        s = torch.cuda.current_stream(device)  # the temporaries above are freed in this stream's order
+        _lib.check(L.hgf_categorical_update(C.byref(c), C.c_void_p(s.cuda_stream)))
     return out

@@ -21,6 +21,7 @@ using namespace hgf;
 
 static_assert(NF == HGF_N_FIELDS, "field count out of sync with the public header");
 static_assert(N_RESP_PARAMS == HGF_N_RESPONSE_PARAMETERS, "response parameter count out of sync");
+static_assert(FUSED_RING == HGF_FUSED_RING, "fused-reduction ring size out of sync with the public header");
 
 static thread_local std::string g_error;
 static std::atomic<long long> g_launches{0};
@@ -54,7 +55,7 @@ int64_t hgf_fused_reduce_bytes(int32_t n_groups, int32_t dtype) {
   return (n_groups < 1 || (dtype != 32 && dtype != 64)) ? -1 : fused_bytes(n_groups, dtype / 8);
 }
 int64_t hgf_fused_reduce_result_offset(int32_t n_groups, int32_t dtype, uint32_t epoch) {
-  return (n_groups < 1 || (dtype != 32 && dtype != 64)) ? -1 : static_cast<int64_t>(epoch & 1u) * n_groups * (dtype / 8);
+  return (n_groups < 1 || (dtype != 32 && dtype != 64)) ? -1 : static_cast<int64_t>(epoch % FUSED_RING) * n_groups * (dtype / 8);
 }
 
 int hgf_plan_create(const hgf_topology_t* t, hgf_plan_t** out) {
@@ -545,8 +546,14 @@ static int run_host_chunked(const hgf_plan_t* plan, const hgf_call_t* c, bool wa
   return 0;
 }
 
-static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, bool want_grad) {
+static int run_host(const hgf_plan_t* plan, const hgf_call_t* c_in, int device, bool want_grad) {
   CallLists lists;
+  // With a fused cross-GPU reduction the sums live in the workspace; the host entry points accept a HOST `reduced`
+  // all the same and deliver the ALL-REDUCED sums there: launch, wait for every rank's deposit, copy the slot out.
+  hgf_call_t c_local = *c_in;
+  void* host_all_reduced = nullptr;
+  if (c_in->world_size > 1 && c_in->reduced) { host_all_reduced = c_in->reduced; c_local.reduced = nullptr; }
+  const hgf_call_t* c = &c_local;
   if (check_call(plan, c, want_grad, lists)) return 1;
   const Program& p = plan->prog;
   const size_t w = c->dtype == 32 ? 4 : 8;
@@ -593,6 +600,13 @@ static int run_host(const hgf_plan_t* plan, const hgf_call_t* c, int device, boo
   d.reduced = st.out(c->reduced, sz_red, true);
   int rc = 0;
   if (st.err == cudaSuccess) rc = launch(plan, &d, g_host.stream, want_grad);
+  if (rc == 0 && st.err == cudaSuccess && host_all_reduced) {
+    void* ws = c->peer_workspace[c->rank];
+    rc = hgf_fused_reduce_wait(ws, c->n_groups, c->dtype, c->world_size, c->epoch, g_host.stream);
+    if (rc == 0)
+      st.err = cudaMemcpyAsync(host_all_reduced, static_cast<char*>(ws) + hgf_fused_reduce_result_offset(c->n_groups, c->dtype, c->epoch),
+                               static_cast<size_t>(c->n_groups) * w, cudaMemcpyDeviceToHost, g_host.stream);
+  }
   st.finish();
   if (rc) return rc;
   if (st.err != cudaSuccess) return fail("host staging failed: %s", cudaGetErrorString(st.err));

@@ -113,8 +113,11 @@ __global__ void __launch_bounds__(128) categorical_kernel(hgf_categorical_call_t
       a2[k] = now.alpha(k);
       sum2 += a2[k];
       now_positive = now_positive && a2[k] > B(0);
-      const B e = HGF_LDG(now.em + k * stride);
-      surprise += HGF_LDG(obs + k) != B(0) ? -log(e) : -log(B(1) - e);  // binary_surprise, summed over the categories
+      // binary_surprise(..., clipping=True), summed over the categories (categorical.py:77-82; math.py:248-253 clips the
+      // expected mean to [1e-6, 1 - 1e-6] itself, whatever the network's precision_clipping_value is)
+      B e = HGF_LDG(now.em + k * stride);
+      e = e < B(1e-6) ? B(1e-6) : (e > B(1.0 - 1e-6) ? B(1.0 - 1e-6) : e);
+      surprise += HGF_LDG(obs + k) != B(0) ? -log(e) : -log(B(1) - e);
       if (c.alpha) static_cast<B*>(c.alpha)[k * stride + i] = a2[k];
       if (c.mean) static_cast<B*>(c.mean)[k * stride + i] = now.updated_mean(k);
     }

@@ -97,15 +97,25 @@ struct CallLists {
   uint16_t param_row[MAX_PARAMS];
 };
 
-// Workspace of the fused cross-GPU reduction, in scalars of width w: result[2][G] (double-buffered by epoch
-// parity), partial[G] (this rank's per-group sums), then two 32-bit words: block ticket counter, peer signal.
+// Workspace of the fused cross-GPU reduction, in scalars of width w:
+//   result[FUSED_RING][G]   the all-reduced sums of launch (epoch) e live in slot e % FUSED_RING
+//   partial[G]              this rank's per-group sums of the running launch
+//   ticket (32-bit word, own cache line)   block counter of the running launch
+//   done[MAX_PEERS] (32-bit words)         done[r] = number of launches rank r has deposited (written by rank r)
+// Protocol (hgf_scan.cuh::fused_deposit): a launch DEPOSITS its sums into every rank's slot and raises its done word
+// on every rank, then EXITS -- it never waits for the other ranks' sums.  Whoever consumes the sums waits
+// (hgf_fused_reduce_wait: a one-block kernel on the consumer's stream).  Ranks may therefore drift apart by up to
+// FUSED_RING / 2 - 1 launches; the only in-kernel wait is that flow control, which a launch passes without spinning
+// unless a peer is that far behind.
+constexpr int FUSED_RING = 16;
 #ifdef __CUDACC__
 #define HGF_PROGRAM_HD __host__ __device__
 #else
 #define HGF_PROGRAM_HD
 #endif
-HGF_PROGRAM_HD constexpr long long fused_ctl_offset(long long G, long long w) { return (3 * G * w + 15) / 16 * 16; }
-HGF_PROGRAM_HD constexpr long long fused_bytes(long long G, long long w) { return fused_ctl_offset(G, w) + 16; }
+HGF_PROGRAM_HD constexpr long long fused_ctl_offset(long long G, long long w) { return ((FUSED_RING + 1) * G * w + 63) / 64 * 64; }
+HGF_PROGRAM_HD constexpr long long fused_done_offset(long long G, long long w) { return fused_ctl_offset(G, w) + 64; }
+HGF_PROGRAM_HD constexpr long long fused_bytes(long long G, long long w) { return fused_done_offset(G, w) + 64; }
 
 // One launch's arguments (device pointers; see hgf_call_t in include/pyhgf_cuda.h).
 struct ScanArgs {

@@ -254,8 +254,13 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
   if (REC && traj && stage && threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem outlives the last store
 #endif
 
-  // response.py:87-89: total_gaussian_surprise is +inf everywhere if node 1's mean ever was NaN
-  if (response_fn == RESP_TOTAL_GAUSSIAN && node1_mean_nan) total = TR(b_inf<B>());
+  // response.py:86-89: total_gaussian_surprise is +inf at EVERY trial if node 1's mean ever was NaN -- the sum, and
+  // the per-trial values already written (a rare, cold rewrite of this instance's column)
+  if (response_fn == RESP_TOTAL_GAUSSIAN && node1_mean_nan) {
+    total = TR(b_inf<B>());
+    if (pointwise && active)
+      for (int t = 0; t < T_steps; ++t) pointwise[static_cast<long long>(t) * N + n] = b_inf<B>();
+  }
 
   const B scale = static_cast<B>(args.out_scale);
   if (active) {
@@ -302,14 +307,18 @@ template <class B> __device__ __forceinline__ void reduce_into_groups(B* reduced
 }
 
 // ---------------------------------------------------------------------------
-// Fused all-reduce of the per-group sums over NVLink peer memory (hgf_call_t::peer_workspace).
-// Every block has added its groups' sums into this rank's `partial`.  The LAST block of the grid (ticket
-// counter) then (1) zeroes the result buffer of the NEXT epoch, (2) adds each partial sum into the current
-// epoch's result buffer of EVERY rank -- one multimem.red through the NVSwitch multicast mapping, or one
-// system-scope red per peer -- (3) fences and raises every peer's signal word, and (4) waits until its own
-// signal shows that all W ranks have contributed.  Peers can only start adding epoch e+1 after seeing this
-// rank's epoch-e signal, which is sent after step (1): that is what makes the double buffer safe without any
-// host-side synchronisation.  Called by every thread of every block, in uniform control flow.
+// Fused all-reduce of the per-group sums over NVLink peer memory (hgf_call_t::peer_workspace; layout and protocol:
+// hgf_program.h).  Every block has added its groups' sums into this rank's `partial`.  The LAST block of the grid
+// (ticket counter) then
+//   (0) flow control: makes sure no peer is more than FUSED_RING / 2 - 1 launches behind (it normally is not, and
+//       nothing spins) -- that is what guarantees that the slot written below was zeroed by its owner;
+//   (1) zeroes this rank's slot of launch e + FUSED_RING / 2;
+//   (2) adds each partial sum into slot e % FUSED_RING of EVERY rank -- one multimem.red through the NVSwitch
+//       multicast mapping, or one system-scope red per peer;
+//   (3) fences and stores e + 1 into its `done` word on every rank;
+// and the kernel ends.  It does NOT wait for the other ranks' sums: a rank that runs ahead is not held back by the
+// launch skew of the others.  The consumer of the sums waits (fused_wait_kernel, hgf_fused_reduce_wait).
+// Called by every thread of every block, in uniform control flow.
 template <class B> __device__ __forceinline__ void red_add_sys(B* p, B v) { atomicAdd_system(p, v); }
 __device__ __forceinline__ void multimem_red(float* p, float v) {
   asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
@@ -317,27 +326,51 @@ __device__ __forceinline__ void multimem_red(float* p, float v) {
 __device__ __forceinline__ void multimem_red(double* p, double v) {
   asm volatile("multimem.red.relaxed.sys.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Spin until done[p] >= want (wrap-safe); false after ~10 s: a peer never arrived.
+__device__ __forceinline__ bool fused_wait_done(const unsigned* done_word, unsigned want) {
+  const long long t0 = clock64();
+  while (static_cast<int>(ld_acquire_sys(done_word) - want) < 0) {
+    if (clock64() - t0 > 20000000000LL) return false;
+  }
+  return true;
+}
 
-template <class B> __device__ __forceinline__ void fused_all_reduce(const ScanArgs& args) {
+template <class B> __device__ __forceinline__ void fused_deposit(const ScanArgs& args) {
   __shared__ int is_last;
   const int G = args.n_groups, W = args.world;
-  B* ws = static_cast<B*>(args.peer_ws[args.rank]);
-  B* partial = ws + 2 * static_cast<size_t>(G);
-  unsigned* ctl = reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(ws) + fused_ctl_offset(G, sizeof(B)));
+  unsigned char* base = static_cast<unsigned char*>(args.peer_ws[args.rank]);
+  B* ws = reinterpret_cast<B*>(base);
+  B* partial = ws + static_cast<size_t>(FUSED_RING) * G;
+  unsigned* ticket = reinterpret_cast<unsigned*>(base + fused_ctl_offset(G, sizeof(B)));
+  const unsigned* done = reinterpret_cast<const unsigned*>(base + fused_done_offset(G, sizeof(B)));
   __syncthreads();  // this block's atomics into `partial` are issued
   if (threadIdx.x == 0) {
     __threadfence();
-    is_last = atomicAdd(ctl, 1u) == gridDim.x - 1;
+    is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
   }
   __syncthreads();
   if (!is_last) return;
   __threadfence();
   const unsigned e = args.epoch;
-  B* next = ws + static_cast<size_t>((e + 1) & 1u) * G;
-  for (int g = threadIdx.x; g < G; g += blockDim.x) next[g] = B(0);
-  const size_t cur = static_cast<size_t>(e & 1u) * G;
+  // (0) every peer has finished launch e - FUSED_RING / 2 (and with it zeroed its slot e % FUSED_RING)
+  bool ok = true;
+  if (e >= FUSED_RING / 2 && static_cast<int>(threadIdx.x) < W) ok = fused_wait_done(done + threadIdx.x, e - FUSED_RING / 2 + 1u);
+  ok = __syncthreads_and(ok);
+  // (1)
+  B* ahead = ws + static_cast<size_t>((e + FUSED_RING / 2) % FUSED_RING) * G;
+  for (int g = threadIdx.x; g < G; g += blockDim.x) ahead[g] = B(0);
+  // (2)
+  const size_t cur = static_cast<size_t>(e % FUSED_RING) * G;
   for (int g = threadIdx.x; g < G; g += blockDim.x) {
-    const B v = __ldcg(partial + g);
+    const B v = ok ? __ldcg(partial + g) : b_nan<B>();  // a peer that never arrived: poison instead of hanging the GPU
     partial[g] = B(0);  // ready for the next launch
     if (args.mc_ws) {
       multimem_red(static_cast<B*>(args.mc_ws) + cur + g, v);
@@ -345,27 +378,28 @@ template <class B> __device__ __forceinline__ void fused_all_reduce(const ScanAr
       for (int p = 0; p < W; ++p) red_add_sys(static_cast<B*>(args.peer_ws[p]) + cur + g, v);
     }
   }
+  // (3)
   __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) {
-    *ctl = 0u;  // ticket counter, for the next launch
-    for (int p = 0; p < W; ++p) {
-      unsigned* peer_ctl = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(args.peer_ws[p]) + fused_ctl_offset(G, sizeof(B)));
-      atomicAdd_system(peer_ctl + 1, 1u);
-    }
-    const unsigned want = static_cast<unsigned>(W) * (e + 1u);
-    const long long t0 = clock64();
-    while (true) {
-      unsigned seen;
-      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(ctl + 1) : "memory");
-      if (static_cast<int>(seen - want) >= 0) break;
-      if (clock64() - t0 > 20000000000LL) {  // ~10 s: a peer never arrived; poison the result instead of hanging the GPU
-        for (int g = 0; g < G; ++g) ws[cur + g] = b_nan<B>();
-        break;
-      }
-    }
+  if (threadIdx.x == 0) *ticket = 0u;  // for the next launch
+  if (static_cast<int>(threadIdx.x) < W) {
+    unsigned* peer_done = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(args.peer_ws[threadIdx.x]) + fused_done_offset(G, sizeof(B)));
+    st_release_sys(peer_done + args.rank, e + 1u);
   }
-  __syncthreads();
+}
+
+// The consumer's side: wait until every rank has deposited launch `epoch` into this rank's workspace.  One block;
+// thread p watches rank p.  A peer that never arrives poisons the slot with NaN after ~10 s.
+template <class B> __global__ void fused_wait_kernel(void* workspace, int G, int W, unsigned epoch) {
+  unsigned char* base = static_cast<unsigned char*>(workspace);
+  const unsigned* done = reinterpret_cast<const unsigned*>(base + fused_done_offset(G, sizeof(B)));
+  bool ok = true;
+  if (static_cast<int>(threadIdx.x) < W) ok = fused_wait_done(done + threadIdx.x, epoch + 1u);
+  ok = __syncthreads_and(ok);
+  if (!ok) {
+    B* slot = reinterpret_cast<B*>(base) + static_cast<size_t>(epoch % FUSED_RING) * G;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) slot[g] = b_nan<B>();
+  }
 }
 
 // Occupancy: BASELINE config 4 gives each GPU 65 536 instances = 13.8 warps per SM; the float32 register-
@@ -391,9 +425,9 @@ scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLi
   const auto total = scan_instance<T, Topo, NSLOTS, PR, UNIT_DT, REC>(prog, lists, args, n, active, stage);
   if (args.world > 1) {
     const int g = args.group ? __ldg(args.group + n) : 0;
-    B* partial = static_cast<B*>(args.peer_ws[args.rank]) + 2 * static_cast<size_t>(args.n_groups);
+    B* partial = static_cast<B*>(args.peer_ws[args.rank]) + static_cast<size_t>(FUSED_RING) * args.n_groups;
     reduce_into_groups<B>(partial, g, static_cast<B>(args.out_scale) * pv(total), active);
-    fused_all_reduce<B>(args);
+    fused_deposit<B>(args);
   } else if (args.reduced) {
     const int g = args.group ? __ldg(args.group + n) : 0;
     reduce_into_groups<B>(static_cast<B*>(args.reduced), g, static_cast<B>(args.out_scale) * pv(total), active);

@@ -57,10 +57,14 @@ class FusedReduce:
     Each rank allocates ``hgf_fused_reduce_bytes`` of symmetric memory (CUDA VMM, mapped into every peer by
     ``torch.distributed._symmetric_memory``); the kernel's last block adds the rank's sums into every peer's copy
     over NVLink (one ``multimem.red`` per value through the NVSwitch multicast mapping when the driver offers one),
-    signals the peers and waits for theirs, so that when the launch completes ``result()`` holds the sums over
-    ALL ranks -- there is no NCCL call on the path.  Pass it to ``Network.batch(..., fused_reduce=...)``; every
-    rank must launch the same number of times (the epoch counter is part of the protocol).
+    publishes "deposited" to every peer and the kernel ends: it never waits for the other ranks, and there is no NCCL
+    call on the path.  The consumer waits: ``result()`` enqueues a one-block kernel on the current stream that
+    returns once every rank's sums of that launch have arrived, and hands back the ``[n_groups]`` view.  Pass the
+    object to ``Network.batch(..., fused_reduce=...)``; every rank must launch the same number of times (the epoch
+    counter is part of the protocol), and ranks may drift apart by up to ``RING // 2 - 1`` launches.
     """
+
+    RING = 16  # HGF_FUSED_RING
 
     def __init__(self, n_groups: int, bits: int = 32, device=None, group: Optional[dist.ProcessGroup] = None,
                  multicast: bool = True):
@@ -110,9 +114,24 @@ class FusedReduce:
         call.reduced = None
         return e
 
-    def result(self, epoch: Optional[int] = None) -> torch.Tensor:
-        """The all-reduced ``[n_groups]`` sums of launch ``epoch`` (default: the last one); valid until the launch after next."""
+    def result(self, epoch: Optional[int] = None, wait: bool = True, stream=None) -> torch.Tensor:
+        """The all-reduced ``[n_groups]`` sums of launch ``epoch`` (default: the last one).  ``wait`` enqueues, on
+        ``stream`` (default: the current one), the wait for every rank's deposit of that launch; work enqueued on
+        that stream afterwards sees the complete sums.  The view stays valid for the next ``RING // 2 - 1``
+        launches on this workspace (the slot is then zeroed for reuse): clone it to keep it longer."""
         e = self.epoch - 1 if epoch is None else epoch
+        if e < 0:
+            raise RuntimeError("no launch has used this workspace yet")
+        if e < self.epoch - (self.RING // 2 - 1):
+            raise RuntimeError(f"the sums of launch {e} have been recycled ({self.epoch} launches so far, {self.RING // 2 - 1} kept)")
+        if wait:
+            from . import _lib
+
+            dev = self.buffer.device
+            with torch.cuda.device(dev):
+                s = torch.cuda.current_stream(dev) if stream is None else stream
+                _lib.check(self._L.hgf_fused_reduce_wait(self.buffer.data_ptr(), self.n_groups, self.bits, self.world_size,
+                                                         e & 0xFFFFFFFF, s.cuda_stream))
         off = int(self._L.hgf_fused_reduce_result_offset(self.n_groups, self.bits, e & 0xFFFFFFFF))
         w = self.bits // 8
         return self.buffer[off:off + self.n_groups * w].view(torch.float32 if self.bits == 32 else torch.float64)

@@ -106,6 +106,7 @@ def launch(*, bits: int, device, series: torch.Tensor, observed, nus, xis0: np.n
     c.xis0 = x0.data_ptr()
     c.xis_trajectory = traj.data_ptr() if traj is not None else None
     c.xis_last = last.data_ptr()
-    s = torch.cuda.current_stream(device)  # the temporaries above are freed in this stream's order
-    _lib.check(L.hgf_ef_filter(C.byref(c), C.c_void_p(s.cuda_stream)))
+    with torch.cuda.device(device):  # the library launches on the CURRENT device: make it the tensors' one
+        s = torch.cuda.current_stream(device)  # the temporaries above are freed in this stream's order
+        _lib.check(L.hgf_ef_filter(C.byref(c), C.c_void_p(s.cuda_stream)))
     return (traj, last) if implied is None else (traj, last, nus_t)

@@ -120,19 +120,21 @@ class BatchResult:
         self.reduced = None
         self.kernel_name = ""
 
-    def relaunch(self, stream=None):
+    def relaunch(self, stream=None, consume: bool = True):
         """Enqueue the same evaluation again on the same device buffers (inputs and outputs stay resident
         in HBM; a sampler or a benchmark overwrites the parameter tensors in place between calls).
-        Host cost: one C call."""
+        Host cost: one C call.  With a fused cross-GPU reduction, ``consume=False`` skips the wait for the other
+        ranks' sums (``self.reduced`` is then only valid after ``fused_reduce.result()`` has been asked for it)."""
         s = torch.cuda.current_stream(self._device) if stream is None else stream
         fused = getattr(self, "_fused", None)
-        if fused is not None:
-            fused.attach(self._call)  # next epoch; the all-reduced sums land in the workspace
-        elif self.reduced is not None:
-            self.reduced.zero_()
-        _lib.check(self._fn(self._plan.handle, C.byref(self._call), C.c_void_p(s.cuda_stream)))
-        if fused is not None:
-            self.reduced = fused.result()
+        with torch.cuda.device(self._device), torch.cuda.stream(s):  # the zeroing is ordered with the kernel, on ITS stream
+            if fused is not None:
+                fused.attach(self._call)  # next epoch; the all-reduced sums land in the workspace
+            elif self.reduced is not None:
+                self.reduced.zero_()
+            _lib.check(self._fn(self._plan.handle, C.byref(self._call), C.c_void_p(s.cuda_stream)))
+            if fused is not None:
+                self.reduced = fused.result(wait=consume, stream=s)
         return self
 
     @property
@@ -154,7 +156,7 @@ class ComponentsResult(BatchResult):
         self._parts, self._streams, self._device = parts, streams, device
         self.kernel_name = f"components({len(parts)}): " + " | ".join(p.kernel_name for p in parts)
 
-    def relaunch(self, stream=None):
+    def relaunch(self, stream=None, consume: bool = True):
         cur = torch.cuda.current_stream(self._device) if stream is None else stream
         for part, s in zip(self._parts, self._streams):
             s.wait_stream(cur)
@@ -651,10 +653,22 @@ class Network:
             obs = (o[:, :, :n_fed] != 0).to(torch.uint8).contiguous()
         return x.contiguous(), obs
 
-    def _launch(self, *, values, observed, time_steps, input_group_size, n_instances, params: dict,
-                response_fn: int, response_inputs, response_group_size, response_parameters, record_slots,
-                want_last, want_sum, want_pointwise, want_grad, group, n_groups, out_scale=1.0, stream=None,
-                attributes=None, fused_reduce=None, generative_seed=None, plan=None, branch_idx=None):
+    def _launch(self, *, values, stream=None, **kw):
+        """Stage, allocate and enqueue one launch.  With ``stream`` given, ALL of it happens in that stream's order
+        (it first waits for what the caller's current stream has enqueued, i.e. for the inputs): staging copies and
+        output allocations made on another stream would race with the kernel."""
+        dev = values.device
+        cur = torch.cuda.current_stream(dev)
+        if stream is not None and stream != cur:
+            stream.wait_stream(cur)
+            with torch.cuda.device(dev), torch.cuda.stream(stream):
+                return self._launch_impl(values=values, stream=stream, **kw)
+        return self._launch_impl(values=values, stream=stream, **kw)
+
+    def _launch_impl(self, *, values, observed, time_steps, input_group_size, n_instances, params: dict,
+                     response_fn: int, response_inputs, response_group_size, response_parameters, record_slots,
+                     want_last, want_sum, want_pointwise, want_grad, group, n_groups, out_scale=1.0, stream=None,
+                     attributes=None, fused_reduce=None, generative_seed=None, plan=None, branch_idx=None):
         L = _lib.lib()
         dev = values.device
         dt = _torch_dtype(self.bits)
@@ -772,7 +786,7 @@ class Network:
         res._last = last
         res._fused = fused_reduce if n_groups else None
         if res._fused is not None:
-            res.reduced = fused_reduce.result()
+            res.reduced = fused_reduce.result(stream=s)
         if grad is not None:
             res.gradient = {k: grad[i] for i, k in enumerate(keys)}
             res._grad = grad
@@ -962,6 +976,17 @@ class Network:
         return self
 
     def _categorical_batch(self, input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream):
+        """Runs ``_categorical_batch_impl`` in ``stream``'s order: the implied scan AND the per-node follow-up launches
+        (which read the scan's trajectories) are enqueued on the same stream."""
+        dev = self.device
+        cur = torch.cuda.current_stream(dev)
+        if stream is not None and stream != cur:
+            stream.wait_stream(cur)
+            with torch.cuda.device(dev), torch.cuda.stream(stream):
+                return self._categorical_batch_impl(input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream)
+        return self._categorical_batch_impl(input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream)
+
+    def _categorical_batch_impl(self, input_data, parameters, time_steps, observed, n_instances, input_group_size, record, stream):
         """``batch`` with categorical / dynamic ef-state nodes: the implied network's batch (fed with the one-hot columns
         or with t(x)), then one launch per vector node that is recorded -- ``(node, "kl_divergence" | "surprise" |
         "alpha" | "mean")`` for a categorical node, ``(node, "xis" | "nus")`` for an ef-state node."""

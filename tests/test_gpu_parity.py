@@ -228,6 +228,27 @@ def test_nan_propagates_like_the_reference(G, R):
     assert np.array_equal(np.isinf(sg), np.isinf(so))
 
 
+def test_total_gaussian_surprise_is_inf_at_every_trial_once_node1_was_nan(G, R, datasets):
+    """pyhgf/response.py:86-89: `jnp.where(jnp.any(jnp.isnan(node_trajectories[1]["mean"])), jnp.inf, surprise)` acts on
+    the whole per-trial vector, not only on its sum -- single network and batched pointwise output alike."""
+    x = datasets["x"][:60].copy()
+    bad = x.copy()
+    bad[30] = np.nan  # a NaN observation: node 1's posterior mean is NaN from trial 30 on, finite before
+    o = nets.continuous3(onet.Network).input_data(bad)
+    want = o.surprise(onet.total_gaussian_surprise)
+    m1 = np.asarray(o.node_trajectories[1]["mean"])
+    assert np.isfinite(m1[:30]).all() and np.isnan(m1[30:]).all() and np.isinf(want).all()
+    g = nets.continuous3(G.Network).input_data(bad)
+    assert np.isinf(g.surprise(R.total_gaussian_surprise)).all()
+    res = nets.continuous3(G.Network).batch(np.stack([x, bad, x]), {(2, "tonic_volatility"): np.array([-2.0, -2.0, -3.0])}, input_group_size=1,
+                                            response_function=R.total_gaussian_surprise, pointwise=True)
+    pw = res.pointwise.cpu().numpy()
+    assert np.isfinite(pw[0]).all() and np.isfinite(pw[2]).all() and np.isinf(pw[1]).all()
+    assert np.isinf(res.surprise.cpu().numpy()[1]) and np.isfinite(res.surprise.cpu().numpy()[[0, 2]]).all()
+    clean = nets.continuous3(onet.Network, om2=-2.0).input_data(x).surprise(onet.total_gaussian_surprise)
+    assert np.allclose(pw[0], clean, rtol=1e-4, atol=1e-4)
+
+
 # ------------------------------------------------------------------ batched surprise and gradients
 def _grid(n, lo=-7.0, hi=-1.0, seed=0):
     rng = np.random.default_rng(seed)
@@ -534,7 +555,7 @@ def test_tma_trajectory_writeback_is_bit_identical(G, datasets, net_name, n, dty
 
 
 def test_fused_all_reduce_two_gpus():
-    """The in-kernel all-reduce over NVLink peer memory against NCCL (tools/test_fused_reduce.py under torchrun):
+    """The in-kernel all-reduce over NVLink peer memory against NCCL (tools/fused_reduce_check.py under torchrun):
     needs two GPUs, so it is skipped on the single-GPU box."""
     import os
     import subprocess
@@ -546,7 +567,7 @@ def test_fused_all_reduce_two_gpus():
         pytest.skip("needs 2 GPUs")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-                        "--master-port", "29533", os.path.join(root, "tools", "test_fused_reduce.py")], capture_output=True, text=True,
+                        "--master-port", "29533", os.path.join(root, "tools", "fused_reduce_check.py")], capture_output=True, text=True,
                        timeout=600, cwd=root)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert '"max_rel_err_vs_nccl"' in r.stdout

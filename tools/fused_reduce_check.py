@@ -1,7 +1,7 @@
 """2+ GPU check (torchrun): the in-kernel all-reduce over peer memory (FusedReduce) against NCCL, for several
 consecutive launches (epochs), with and without the multicast mapping; then both timed on BASELINE config 4's shape.
 
-    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/test_fused_reduce.py
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/fused_reduce_check.py
 """
 import os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
