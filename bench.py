@@ -541,7 +541,7 @@ def run_gpu(args):
     w_e2e.evals_per_step = R
     e2e_dt, h2d, d2h, e2e_logp, e2e_red = e2e_leg(w_e2e, e2e_steps, min(max(args.warmup, 1), 3), local, fused)
     same = None if (e2e_logp is None or w_e2e is not w) else bool(np.allclose(e2e_logp, res.surprise.cpu().numpy(), rtol=1e-6, equal_nan=True))
-    if e2e_red is not None and world > 1:
+    if e2e_red is not None and world > 1 and fused is not None:
         torch.cuda.synchronize()
         same = bool(same and np.allclose(e2e_red, res.reduced.cpu().numpy(), rtol=1e-5))  # the host call returned the ALL-REDUCED sums
     t2 = torch.tensor([e2e_dt / e2e_steps], device=dev, dtype=torch.float64)
