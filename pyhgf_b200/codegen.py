@@ -181,7 +181,7 @@ def generate_header(name, g, vol_updates, mean_field, inputs=None) -> str:
         "// Compile-time answers to the topology queries of hgf_ops.cuh; do not edit.\n",
         "#pragma once\n#include \"hgf_ops.cuh\"\n\nnamespace hgf {\n\n",
         f"struct Topo_{name} {{\n",
-        "  static constexpr bool is_static = true;\n  static constexpr int kUnroll = 256;\n",
+        "  static constexpr bool is_static = true;\n  static constexpr bool kConstAttributes = false;\n  static constexpr int kUnroll = 256;\n",
         f"  static constexpr int kSlots = {n_slots};\n  static constexpr int kNodes = {n};\n",
         "  const Program& p;\n",
         f"  HGF_D explicit Topo_{name}(const Program& prog) : p(prog) {{}}\n",
@@ -212,12 +212,13 @@ def generate_header(name, g, vol_updates, mean_field, inputs=None) -> str:
         out.append(_switch(fn, ["n", "k"], t[fn]))
     # the schedule as straight-line code: every op and node index is a literal, so the switch in apply_op and
     # the edge loops inside the update functions resolve at compile time without relying on loop unrolling
-    out.append("  template <class T> HGF_D void run_predictions(T* s, const Step<T>& st) const {\n")
+    # (`self` is the accessor the kernel was instantiated with: this struct or a wrapper such as ConstAttributes<>)
+    out.append("  template <class T, class Self> HGF_D void run_predictions(const Self& self, T* s, const Step<T>& st) const {\n")
     for node, fn in pred:
-        out.append(f"    apply_op(*this, s, st, {fn.opcode}, {node});  // {fn.__name__}\n")
-    out.append("  }\n  template <class T> HGF_D void run_updates(T* s, const Step<T>& st) const {\n")
+        out.append(f"    apply_op(self, s, st, {fn.opcode}, {node});  // {fn.__name__}\n")
+    out.append("  }\n  template <class T, class Self> HGF_D void run_updates(const Self& self, T* s, const Step<T>& st) const {\n")
     for node, fn in upd:
-        out.append(f"    apply_op(*this, s, st, {fn.opcode}, {node});  // {fn.__name__}\n")
+        out.append(f"    apply_op(self, s, st, {fn.opcode}, {node});  // {fn.__name__}\n")
     out.append("  }\n};\n\n}  // namespace hgf\n")
     return "".join(out)
 

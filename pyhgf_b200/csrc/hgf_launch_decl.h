@@ -4,11 +4,10 @@
 #include <cuda_runtime.h>
 
 #include "hgf_math.cuh"
+#include "hgf_ops.cuh"  // RuntimeTopo, ConstAttributes<>
 #include "hgf_program.h"
 
 namespace hgf {
-
-struct RuntimeTopo;
 
 // One kernel launch: the filter runs on T = Dual<B, PF>; PR extra tangent directions live only
 // inside the response function.  Defined (and explicitly instantiated) in hgf_launch.cuh users.
@@ -18,11 +17,18 @@ cudaError_t launch_one(const Program& prog, const CallLists& lists, const ScanAr
 // Which (PF, PR) kernels of a (topology, base type) were instantiated: bit PF + 5 * PR.
 constexpr unsigned variant_bit(int pf, int pr) { return 1u << (pf + 5 * pr); }
 
+// `const_attrs`: no structural attribute (autoconnection strength, tonic drift, couplings, clipping value) is among the
+// differentiated parameters of this pass: the register-resident kernels then run their ConstAttributes<> flavour.
 template <class B, class Topo, int NSLOTS, unsigned MASK>
-cudaError_t launch_variant(int pf, int pr, const Program& prog, const CallLists& lists, const ScanArgs& args, cudaStream_t stream) {
+cudaError_t launch_variant(int pf, int pr, bool const_attrs, const Program& prog, const CallLists& lists, const ScanArgs& args, cudaStream_t stream) {
 #define HGF_TRY(PF_, PR_)                                                                  \
   if constexpr ((MASK & variant_bit(PF_, PR_)) != 0) {                                     \
-    if (pf == PF_ && pr == PR_) return launch_one<Dual<B, PF_>, Topo, NSLOTS, PR_>(prog, lists, args, stream); \
+    if (pf == PF_ && pr == PR_) {                                                          \
+      if constexpr (Topo::is_static && PF_ > 0) {                                          \
+        if (const_attrs) return launch_one<Dual<B, PF_>, ConstAttributes<Topo>, NSLOTS, PR_>(prog, lists, args, stream); \
+      }                                                                                    \
+      return launch_one<Dual<B, PF_>, Topo, NSLOTS, PR_>(prog, lists, args, stream);       \
+    }                                                                                      \
   }
   HGF_TRY(0, 0) HGF_TRY(1, 0) HGF_TRY(2, 0) HGF_TRY(3, 0) HGF_TRY(4, 0)
   HGF_TRY(0, 1) HGF_TRY(1, 1) HGF_TRY(2, 1) HGF_TRY(3, 1) HGF_TRY(4, 1)
@@ -45,7 +51,7 @@ cudaError_t launch_scan(const Program& prog, const CallLists& lists_in, const Sc
   if (!want_grad) {
     if ((MASK & 1u) == 0) return cudaErrorNotSupported;
     ++*n_launched;
-    return launch_variant<B, Topo, NSLOTS, MASK>(0, 0, prog, lists, a, stream);
+    return launch_variant<B, Topo, NSLOTS, MASK>(0, 0, false, prog, lists, a, stream);
   }
   if (a.trajectories || a.last_attributes) {
     // trajectories / final attributes of a gradient call: one plain-filter pass (the recording kernels carry no tangents)
@@ -54,12 +60,20 @@ cudaError_t launch_scan(const Program& prog, const CallLists& lists_in, const Sc
     f.surprise_sum = nullptr; f.surprise_pointwise = nullptr; f.gradient = nullptr; f.reduced = nullptr; f.world = 0; f.response_fn = RESP_NONE;
     CallLists fl = lists;
     fl.n_filter = fl.n_params;
-    const cudaError_t err = launch_variant<B, Topo, NSLOTS, MASK>(0, 0, prog, fl, f, stream);
+    const cudaError_t err = launch_variant<B, Topo, NSLOTS, MASK>(0, 0, false, prog, fl, f, stream);
     ++*n_launched;
     if (err != cudaSuccess) return err;
     a.trajectories = nullptr; a.traj_rows = 0; a.last_attributes = nullptr;
   }
   const int F = lists.n_filter, R = lists.n_params - lists.n_filter;
+  // are all differentiated filter parameters beliefs / volatilities / response parameters (hgf_ops.cuh::attr)?
+  bool const_attrs = true;
+  for (int q = 0; q < F; ++q) {
+    const int slot = lists.param_slot[q];
+    const bool node_field = slot < prog.n_nodes * NF;
+    const int field = slot % NF;
+    if (node_field ? (field == F_AUTOCONNECTION_STRENGTH || field == F_TONIC_DRIFT || field == F_OBSERVED) : slot < prog.slot_resp) const_attrs = false;
+  }
   int done_f = 0, done_r = 0;
   while (done_f < F || done_r < R) {
     const int remf = F - done_f;
@@ -75,7 +89,7 @@ cudaError_t launch_scan(const Program& prog, const CallLists& lists_in, const Sc
     if (pf < 0) return cudaErrorNotSupported;
     a.tangent_offset = done_f;
     a.resp_index = pr ? F + done_r : -1;
-    const cudaError_t err = launch_variant<B, Topo, NSLOTS, MASK>(pf, pr, prog, lists, a, stream);
+    const cudaError_t err = launch_variant<B, Topo, NSLOTS, MASK>(pf, pr, const_attrs, prog, lists, a, stream);
     ++*n_launched;
     if (err != cudaSuccess) return err;
     done_f += pf < remf ? pf : remf;

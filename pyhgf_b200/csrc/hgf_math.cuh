@@ -494,6 +494,12 @@ template <class T> HGF_D T x_max(const T& a, const T& b) {
   return (pv(a) >= pv(b)) ? a : b;
 }
 template <class T> HGF_D T x_clip(const T& x, const T& lo, const T& hi) { return x_min(x_max(x, lo), hi); }
+// The same against a bound held in the base type (a constant, never NaN): one comparison instead of three, same ties
+// (the first argument wins) and the same NaN propagation from the variable argument.
+template <class B, int P> HGF_D Dual<B, P> x_min(const Dual<B, P>& a, B b) { return (a.v > b) ? Dual<B, P>(b) : a; }
+template <class B, int P> HGF_D Dual<B, P> x_max(const Dual<B, P>& a, B b) { return (a.v < b) ? Dual<B, P>(b) : a; }
+template <class B, int P> HGF_D Dual<B, P> x_max(B a, const Dual<B, P>& b) { return (b.v <= a) ? Dual<B, P>(a) : b; }
+template <class B, int P> HGF_D Dual<B, P> x_clip(const Dual<B, P>& x, B lo, B hi) { return x_min(x_max(x, lo), hi); }
 template <class T> HGF_D bool x_isfinite(const T& a) { return b_isfinite(pv(a)); }
 template <class T> HGF_D bool x_isnan(const T& a) { return b_isnan(pv(a)); }
 

@@ -16,6 +16,7 @@ namespace hgf {
 
 struct RuntimeTopo {
   static constexpr bool is_static = false;
+  static constexpr bool kConstAttributes = false;
   static constexpr int kUnroll = 1;  // interpreter: keep the schedule and edge loops rolled
   const Program& p;
   HGF_D explicit RuntimeTopo(const Program& prog) : p(prog) {}
@@ -59,9 +60,27 @@ struct RuntimeTopo {
 // The time step of the current slice and its logarithm (the "unbounded" update works in log
 // space); computed once per slice by the scan -- and folded to (1, 0) when the call has no
 // time_steps vector.
+// The time step is data, never a differentiated parameter: it is held in the base type, so that a Dual filter spends no
+// tangent arithmetic on it.
 template <class T> struct Step {
-  T dt, log_dt;
+  base_t<T> dt, log_dt;
 };
+
+// Attributes that are PARAMETERS OF THE MODEL'S STRUCTURE -- autoconnection strength, tonic drift, coupling strengths, the
+// clipping value -- are read through attr().  The general kernels return the full scalar (such a slot may be a
+// differentiated per-instance parameter); a topology accessor wrapped in ConstAttributes<> promises that the call
+// differentiates none of them (the usual case: gradients wrt tonic volatilities / initial beliefs / response parameters)
+// and gets the bare primal, so that every product with them costs 1 + P instructions instead of 1 + 2 P and their
+// tangent registers disappear.  Primal arithmetic is identical in both flavours.
+template <class T, class A> HGF_D auto attr(const A&, const T* s, int idx) {
+  if constexpr (A::kConstAttributes) return pv(s[idx]); else return s[idx];
+}
+template <class Topo> struct ConstAttributes : Topo {
+  static constexpr bool kConstAttributes = true;
+  HGF_D explicit ConstAttributes(const Program& prog) : Topo(prog) {}
+};
+// the `observed` flag of a node is data
+#define HGF_OBSERVED(node) pv(HGF_S(node, F_OBSERVED))
 
 // ---------------------------------------------------------------------------
 // coupling functions g, g', g''.  The reference differentiates the user's
@@ -72,7 +91,7 @@ template <class T> struct Step {
 template <class T> HGF_D T cf_value(int fn, const T& x) {
   using B = base_t<T>;
   switch (fn) {
-    case CF_RELU: return x_max(x, T(B(0)));
+    case CF_RELU: return x_max(x, B(0));
     case CF_SIGMOID: return x_sigmoid(x);
     case CF_TANH: return x_tanh(x);
     case CF_LEAKY_RELU: return (pv(x) >= B(0)) ? x : x * B(0.01);
@@ -127,7 +146,7 @@ template <class T, class A> HGF_D void predict_binary(const A& a, T* s, int node
 #else
   mu = x_sigmoid(mu);
 #endif
-  const T c = s[a.slot_clip()];
+  const auto c = attr(a, s, a.slot_clip());
   mu = x_clip(mu, c, B(1) - c);
   HGF_S(node, F_EXPECTED_MEAN) = mu;
   HGF_S(node, F_EXPECTED_PRECISION) = mu * (B(1) - mu);
@@ -137,15 +156,20 @@ template <class T, class A> HGF_D void predict_binary(const A& a, T* s, int node
 // which has no tonic drift).
 template <class T, class A> HGF_D T predicted_mean(const A& a, const T* s, const Step<T>& st, int node, bool is_volatile) {
   using B = base_t<T>;
-  T drift = is_volatile ? T(B(0)) : HGF_S(node, F_TONIC_DRIFT);
+  const auto lambda = attr(a, s, node * NF + F_AUTOCONNECTION_STRENGTH);
+  if (a.n_vp(node) == 0) {  // no value parents: the drift is the tonic drift alone (same operations, fewer scalar types)
+    if (is_volatile) return lambda * HGF_S(node, F_MEAN) + st.dt * T(B(0));
+    return lambda * HGF_S(node, F_MEAN) + st.dt * attr(a, s, node * NF + F_TONIC_DRIFT);
+  }
+  T drift = is_volatile ? T(B(0)) : T(attr(a, s, node * NF + F_TONIC_DRIFT));
 #pragma unroll (A::kUnroll)
   for (int k = 0; k < a.n_vp(node); ++k) {
     const int par = a.vp(node, k);
     const int fn = a.vp_fn(node, k);
     const T mu_par = HGF_S(par, F_EXPECTED_MEAN);
-    drift = drift + s[a.slot_cvp(node, k)] * (fn == CF_LINEAR ? mu_par : cf_value(fn, mu_par));
+    drift = drift + attr(a, s, a.slot_cvp(node, k)) * (fn == CF_LINEAR ? mu_par : cf_value(fn, mu_par));
   }
-  return HGF_S(node, F_AUTOCONNECTION_STRENGTH) * HGF_S(node, F_MEAN) + st.dt * drift;
+  return lambda * HGF_S(node, F_MEAN) + st.dt * drift;
 }
 
 // Laplace term of the value parents, prediction/continuous.py:240-257.
@@ -157,7 +181,7 @@ template <class T, class A> HGF_D T value_parent_variance(const A& a, const T* s
     const int par = a.vp(node, k);
     const int fn = a.vp_fn(node, k);
     const T slope = (fn == CF_LINEAR) ? T(B(1)) : cf_prime(fn, HGF_S(par, F_EXPECTED_MEAN));
-    const T c = st.dt * s[a.slot_cvp(node, k)] * slope;
+    const T c = st.dt * attr(a, s, a.slot_cvp(node, k)) * slope;
     var = var + (c * c) / HGF_S(par, F_EXPECTED_PRECISION);
   }
   return var;
@@ -180,7 +204,7 @@ template <class T, class A> HGF_D void predict_continuous(const A& a, T* s, cons
 #pragma unroll (A::kUnroll)
   for (int k = 0; k < a.n_volp(node); ++k) {
     const int par = a.volp(node, k);
-    const T kappa = s[a.slot_cvolp(node, k)];
+    const auto kappa = attr(a, s, a.slot_cvolp(node, k));
     log_vol = log_vol + kappa * HGF_S(par, F_EXPECTED_MEAN);
     if (!mean_field) log_vol = log_vol + (kappa * kappa) / (B(2) * HGF_S(par, F_EXPECTED_PRECISION));  // MGF term
   }
@@ -250,7 +274,7 @@ template <class T, class A> HGF_D void predict_volatile(const A& a, T* s, const 
 template <class T> HGF_D void pe_binary(T* s, int node) {
   const T pi_hat = HGF_S(node, F_EXPECTED_PRECISION);
   HGF_S(node, F_VALUE_PREDICTION_ERROR) =
-      ((HGF_S(node, F_MEAN) - HGF_S(node, F_EXPECTED_MEAN)) * HGF_S(node, F_OBSERVED)) / pi_hat;
+      ((HGF_S(node, F_MEAN) - HGF_S(node, F_EXPECTED_MEAN)) * HGF_OBSERVED(node)) / pi_hat;
   HGF_S(node, F_PRECISION) = pi_hat;
 }
 
@@ -303,7 +327,7 @@ template <class T, class A> HGF_D T child_gain_precision(const A& a, const T* s,
 
 // eHGF re-predicted volatility increment,
 // posterior_update_precision_continuous_node.py:564-624.
-template <class T> HGF_D T ehgf_increment(const T* s, const Step<T>& st, int node, int child, const T& kappa) {
+template <class T, class K> HGF_D T ehgf_increment(const T* s, const Step<T>& st, int node, int child, const K& kappa) {
   using B = base_t<T>;
   const T prev_var = HGF_S(child, F_CURRENT_VARIANCE);
   const T omega = st.dt * x_exp(kappa * HGF_S(node, F_MEAN) + HGF_S(child, F_TONIC_VOLATILITY));
@@ -312,8 +336,8 @@ template <class T> HGF_D T ehgf_increment(const T* s, const Step<T>& st, int nod
   const T weight = (omega - prev_var) * pi_hat;
   const T delta = HGF_S(child, F_MEAN) - HGF_S(child, F_EXPECTED_MEAN);
   const T vope = (B(1) / HGF_S(child, F_PRECISION) + delta * delta) * pi_hat - B(1);
-  const T inc = x_max(T(B(0)), B(0.5) * (kappa * kappa) * gamma * (gamma + weight * vope));
-  return inc * HGF_S(child, F_OBSERVED);
+  const T inc = x_max(B(0), B(0.5) * (kappa * kappa) * gamma * (gamma + weight * vope));
+  return inc * HGF_OBSERVED(child);
 }
 
 // posterior_update_precision_continuous_node (+ mean-field, + eHGF forms),
@@ -324,13 +348,13 @@ HGF_D T posterior_precision(const A& a, const T* s, const Step<T>& st, int node,
   using B = base_t<T>;
   bool any_observed = false;
 #pragma unroll (A::kUnroll)
-  for (int k = 0; k < a.n_vc(node); ++k) any_observed = any_observed || (pv(HGF_S(a.vc(node, k), F_OBSERVED)) != B(0));
+  for (int k = 0; k < a.n_vc(node); ++k) any_observed = any_observed || (HGF_OBSERVED(a.vc(node, k)) != B(0));
 #pragma unroll (A::kUnroll)
-  for (int k = 0; k < a.n_volc(node); ++k) any_observed = any_observed || (pv(HGF_S(a.volc(node, k), F_OBSERVED)) != B(0));
+  for (int k = 0; k < a.n_volc(node); ++k) any_observed = any_observed || (HGF_OBSERVED(a.volc(node, k)) != B(0));
   if (!any_observed) {
     T log_vol = HGF_S(node, F_TONIC_VOLATILITY);
 #pragma unroll (A::kUnroll)
-    for (int k = 0; k < a.n_volp(node); ++k) log_vol = log_vol + s[a.slot_cvolp(node, k)] * HGF_S(a.volp(node, k), F_MEAN);
+    for (int k = 0; k < a.n_volp(node); ++k) log_vol = log_vol + attr(a, s, a.slot_cvolp(node, k)) * HGF_S(a.volp(node, k), F_MEAN);
     return B(1) / (B(1) / HGF_S(node, F_PRECISION) + st.dt * x_exp(log_vol));
   }
   T from_values = T(B(0));
@@ -338,21 +362,21 @@ HGF_D T posterior_precision(const A& a, const T* s, const Step<T>& st, int node,
   for (int k = 0; k < a.n_vc(node); ++k) {
     const int child = a.vc(node, k);
     const int fn = a.vc_fn(node, k);
-    const T psi = s[a.slot_cvc(node, k)];
+    const auto psi = attr(a, s, a.slot_cvc(node, k));
     T curvature;
     if (fn == CF_LINEAR) {
-      curvature = psi * psi;
+      curvature = T(psi * psi);
     } else {
       const T g1 = cf_prime(fn, HGF_S(node, F_MEAN));
       curvature = (psi * psi) * (g1 * g1) - psi * cf_second(fn, HGF_S(node, F_MEAN)) * HGF_S(child, F_VALUE_PREDICTION_ERROR);
     }
-    from_values = from_values + child_precision_weight(a, s, child, mean_field) * curvature * HGF_S(child, F_OBSERVED);
+    from_values = from_values + child_precision_weight(a, s, child, mean_field) * curvature * HGF_OBSERVED(child);
   }
   T from_volatility = T(B(0));
 #pragma unroll (A::kUnroll)
   for (int k = 0; k < a.n_volc(node); ++k) {
     const int child = a.volc(node, k);
-    const T kappa = s[a.slot_cvolc(node, k)];
+    const auto kappa = attr(a, s, a.slot_cvolc(node, k));
     if (ehgf) {
       from_volatility = from_volatility + ehgf_increment(s, st, node, child, kappa);
     } else {  // :142-173
@@ -360,7 +384,7 @@ HGF_D T posterior_precision(const A& a, const T* s, const Step<T>& st, int node,
       const T vope = HGF_S(child, F_VOLATILITY_PREDICTION_ERROR);
       const T kg = kappa * gamma;
       from_volatility = from_volatility +
-                        (B(0.5) * (kg * kg) + (kg * kg) * vope - B(0.5) * (kappa * kappa) * gamma * vope) * HGF_S(child, F_OBSERVED);
+                        (B(0.5) * (kg * kg) + (kg * kg) * vope - B(0.5) * (kappa * kappa) * gamma * vope) * HGF_OBSERVED(child);
     }
   }
   return nan_unless_positive(HGF_S(node, F_EXPECTED_PRECISION) + (from_values + from_volatility));
@@ -375,17 +399,21 @@ HGF_D T posterior_mean(const A& a, const T* s, int node, const T& node_precision
   for (int k = 0; k < a.n_vc(node); ++k) {
     const int child = a.vc(node, k);
     const int fn = a.vc_fn(node, k);
-    const T psi = s[a.slot_cvc(node, k)];
-    const T vape = HGF_S(child, F_VALUE_PREDICTION_ERROR) * HGF_S(child, F_OBSERVED);
-    const T slope = (fn == CF_LINEAR) ? T(B(1)) : cf_prime(fn, HGF_S(node, F_MEAN));
-    from_values = from_values + ((psi * child_gain_precision(a, s, child, mean_field) * slope) / node_precision) * vape;
+    const auto psi = attr(a, s, a.slot_cvc(node, k));
+    const T vape = HGF_S(child, F_VALUE_PREDICTION_ERROR) * HGF_OBSERVED(child);
+    if (fn == CF_LINEAR) {  // slope 1: x * 1 = x bit for bit, and no tangent arithmetic is spent on the constant
+      from_values = from_values + ((psi * child_gain_precision(a, s, child, mean_field)) / node_precision) * vape;
+    } else {
+      const T slope = cf_prime(fn, HGF_S(node, F_MEAN));
+      from_values = from_values + ((psi * child_gain_precision(a, s, child, mean_field) * slope) / node_precision) * vape;
+    }
   }
 #pragma unroll (A::kUnroll)
   for (int k = 0; k < a.n_volc(node); ++k) {
     const int child = a.volc(node, k);
-    T w = s[a.slot_cvolc(node, k)] * HGF_S(child, F_EFFECTIVE_PRECISION) * HGF_S(child, F_VOLATILITY_PREDICTION_ERROR);
+    T w = attr(a, s, a.slot_cvolc(node, k)) * HGF_S(child, F_EFFECTIVE_PRECISION) * HGF_S(child, F_VOLATILITY_PREDICTION_ERROR);
     w = w * (B(1) / (B(2) * node_precision));
-    from_volatility = from_volatility + w * HGF_S(child, F_OBSERVED);
+    from_volatility = from_volatility + w * HGF_OBSERVED(child);
   }
   return HGF_S(node, F_EXPECTED_MEAN) + from_values + from_volatility;
 }
@@ -393,7 +421,7 @@ HGF_D T posterior_mean(const A& a, const T* s, int node, const T& node_precision
 // continuous_node_posterior_update.py:20-128: precision, then mean.
 template <class T, class A> HGF_D void posterior_continuous(const A& a, T* s, const Step<T>& st, int node, bool mean_field) {
   using B = base_t<T>;
-  const T pi = x_min(posterior_precision(a, s, st, node, mean_field, false), T(static_cast<B>(a.max_posterior_precision())));
+  const T pi = x_min(posterior_precision(a, s, st, node, mean_field, false), static_cast<B>(a.max_posterior_precision()));
   HGF_S(node, F_PRECISION) = pi;
   HGF_S(node, F_MEAN) = posterior_mean(a, s, node, pi, mean_field);
 }
@@ -404,7 +432,7 @@ template <class T, class A> HGF_D void posterior_continuous_ehgf(const A& a, T* 
   using B = base_t<T>;
   HGF_S(node, F_MEAN) = posterior_mean(a, s, node, HGF_S(node, F_EXPECTED_PRECISION), mean_field);
   HGF_S(node, F_PRECISION) =
-      x_min(posterior_precision(a, s, st, node, mean_field, true), T(static_cast<B>(a.max_posterior_precision())));
+      x_min(posterior_precision(a, s, st, node, mean_field, true), static_cast<B>(a.max_posterior_precision()));
 }
 
 // Quantities of the "unbounded" volatility-parent update that the child node
@@ -419,21 +447,22 @@ template <class T> struct VolatilityChild {
 // child) and volatile_node_posterior_update_unbounded.py:12-178 (kappa = 1, no
 // omega: EXPLICIT = false).  mu_hat / pi_hat are the volatility parent's (or
 // implicit volatility level's) prediction.
-template <bool EXPLICIT, class T>
-HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, const T& mu_hat, const T& pi_hat, const T& kappa,
+template <bool EXPLICIT, class T, class K>
+HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, const T& mu_hat, const T& pi_hat, const K& kappa,
                              const T& omega, T& post_precision, T& post_mean) {
   using B = base_t<T>;
-  const T prev_var = x_max(c.prev_variance, T(static_cast<B>(1e-128)));
+  const T prev_var = x_max(c.prev_variance, static_cast<B>(1e-128));
   const T delta = c.mean - c.expected_mean;
   const T be = B(1) / c.precision + delta * delta;  // E[(x - mu_hat)^2] under the child's posterior
-  const T log_dt = st.log_dt;
+  const B log_dt = st.log_dt;
   const T log_prev_var = x_log(prev_var);
-  const T gamma = EXPLICIT ? (log_dt + kappa * mu_hat + omega) : (log_dt + mu_hat);
+  T gamma;
+  if constexpr (EXPLICIT) gamma = log_dt + kappa * mu_hat + omega; else gamma = log_dt + mu_hat;
   // expansion 1: around the prediction
   const T w1 = x_sigmoid(gamma - log_prev_var);
   const T da1 = c.expected_precision * be - B(1);
   T pi1, mu1, pi_y;
-  if (EXPLICIT) {
+  if constexpr (EXPLICIT) {
     pi1 = pi_hat + B(0.5) * (kappa * kappa) * w1 * (B(1) - w1);
     mu1 = mu_hat + (kappa * w1 / (B(2) * pi1)) * da1;
     pi_y = pi_hat / (kappa * kappa);
@@ -444,10 +473,10 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   }
   // expansion 2: around the Lambert-W mode
   const T log_w_arg = x_log(be) - x_log(B(2) * pi_y) + B(0.5) / pi_y - gamma;
-  const T w_arg = x_exp(x_min(log_w_arg, T(b_log_max<B>())));
+  const T w_arg = x_exp(x_min(log_w_arg, b_log_max<B>()));
   const T y_star = gamma + x_lambert_w0(w_arg) - B(0.5) / pi_y;
   T x_star, log_s2;
-  if (EXPLICIT) {
+  if constexpr (EXPLICIT) {
     x_star = (y_star - log_dt - omega) / kappa;
     log_s2 = log_dt + kappa * x_star + omega;
   } else {
@@ -458,8 +487,8 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   const T w2 = x_sigmoid(log_s2 - log_prev_var);
   const T da2 = be * x_exp(-log_den) - B(1);
   T pi2_full, pi2_alt;
-  if (EXPLICIT) {
-    const T k2 = kappa * kappa;
+  if constexpr (EXPLICIT) {
+    const auto k2 = kappa * kappa;
     pi2_full = pi_hat + B(0.5) * k2 * w2 * (w2 + (B(2) * w2 - B(1)) * da2);
     pi2_alt = pi_hat + B(0.5) * k2 * w2 * (B(1) - w2);
   } else {
@@ -467,18 +496,22 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
     pi2_alt = pi_hat + B(0.5) * w2 * (B(1) - w2);
   }
   const T pi2_safe = x_where(pv(pi2_full) <= B(0), pi2_alt, pi2_full);
-  const T mu2_safe = EXPLICIT ? x_star + (B(0.5) * kappa * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe
-                              : x_star + (B(0.5) * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe;
+  T mu2_safe;
+  if constexpr (EXPLICIT) mu2_safe = x_star + (B(0.5) * kappa * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe;
+  else mu2_safe = x_star + (B(0.5) * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe;
   // fall back to expansion 1 wherever expansion 2 is not finite ("double where",
   // continuous_node_posterior_update_unbounded.py:173-177)
   const bool ok = x_isfinite(pi2_safe) && x_isfinite(mu2_safe);
   const T pi2 = x_where(ok, pi2_safe, pi1);
   const T mu2 = x_where(ok, mu2_safe, mu1);
   // variational energies at both candidate means
-  const T l1 = x_logaddexp(log_prev_var, EXPLICIT ? (log_dt + kappa * mu1 + omega) : (log_dt + mu1));
+  T arg1, arg2;
+  if constexpr (EXPLICIT) { arg1 = log_dt + kappa * mu1 + omega; arg2 = log_dt + kappa * mu2 + omega; }
+  else { arg1 = log_dt + mu1; arg2 = log_dt + mu2; }
+  const T l1 = x_logaddexp(log_prev_var, arg1);
   const T e1 = mu1 - mu_hat;
   const T i1 = B(-0.5) * l1 - B(0.5) * be * x_exp(-l1) - B(0.5) * pi_hat * (e1 * e1);
-  const T l2 = x_logaddexp(log_prev_var, EXPLICIT ? (log_dt + kappa * mu2 + omega) : (log_dt + mu2));
+  const T l2 = x_logaddexp(log_prev_var, arg2);
   const T e2 = mu2 - mu_hat;
   const T i2 = B(-0.5) * l2 - B(0.5) * be * x_exp(-l2) - B(0.5) * pi_hat * (e2 * e2);
   const T b = x_sigmoid(i2 - i1);
@@ -500,9 +533,9 @@ template <class T, class A> HGF_D void posterior_continuous_unbounded(const A& a
   c.expected_mean = HGF_S(child, F_EXPECTED_MEAN);
   c.expected_precision = HGF_S(child, F_EXPECTED_PRECISION);
   T pi, mu;
-  unbounded_mixture<true>(st, c, HGF_S(node, F_EXPECTED_MEAN), HGF_S(node, F_EXPECTED_PRECISION), s[a.slot_cvolc(node, 0)],
+  unbounded_mixture<true>(st, c, HGF_S(node, F_EXPECTED_MEAN), HGF_S(node, F_EXPECTED_PRECISION), attr(a, s, a.slot_cvolc(node, 0)),
                           HGF_S(child, F_TONIC_VOLATILITY), pi, mu);
-  HGF_S(node, F_PRECISION) = x_min(pi, T(static_cast<B>(a.max_posterior_precision())));
+  HGF_S(node, F_PRECISION) = x_min(pi, static_cast<B>(a.max_posterior_precision()));
   HGF_S(node, F_MEAN) = mu;
 }
 
@@ -521,7 +554,7 @@ template <class T, class A> HGF_D void posterior_volatile(const A& a, T* s, int 
   for (int k = 0; k < a.n_vc(node); ++k) {
     const int child = a.vc(node, k);
     const int fn = a.vc_fn(node, k);
-    const T psi = s[a.slot_cvc(node, k)];
+    const auto psi = attr(a, s, a.slot_cvc(node, k));
     const T w = child_precision_weight(a, s, child, mean_field);
     if (fn == CF_LINEAR) {
       pi = pi + (psi * psi) * w;
@@ -531,16 +564,20 @@ template <class T, class A> HGF_D void posterior_volatile(const A& a, T* s, int 
       pi = pi + w * ((psi * psi) * (g1 * g1) - psi * g2 * HGF_S(child, F_VALUE_PREDICTION_ERROR));
     }
   }
-  pi = x_clip(pi, pi_hat, T(static_cast<B>(a.max_posterior_precision())));
+  pi = x_min(x_max(pi, pi_hat), static_cast<B>(a.max_posterior_precision()));
   HGF_S(node, F_PRECISION) = pi;
   T gain = T(B(0));
 #pragma unroll (A::kUnroll)
   for (int k = 0; k < a.n_vc(node); ++k) {
     const int child = a.vc(node, k);
     const int fn = a.vc_fn(node, k);
-    const T slope = (fn == CF_LINEAR) ? T(B(1)) : cf_prime(fn, HGF_S(node, F_EXPECTED_MEAN));
-    gain = gain + ((s[a.slot_cvc(node, k)] * child_gain_precision(a, s, child, mean_field) * slope) / pi) *
-                      HGF_S(child, F_VALUE_PREDICTION_ERROR);
+    if (fn == CF_LINEAR) {
+      gain = gain + ((attr(a, s, a.slot_cvc(node, k)) * child_gain_precision(a, s, child, mean_field)) / pi) * HGF_S(child, F_VALUE_PREDICTION_ERROR);
+    } else {
+      const T slope = cf_prime(fn, HGF_S(node, F_EXPECTED_MEAN));
+      gain = gain + ((attr(a, s, a.slot_cvc(node, k)) * child_gain_precision(a, s, child, mean_field) * slope) / pi) *
+                        HGF_S(child, F_VALUE_PREDICTION_ERROR);
+    }
   }
   HGF_S(node, F_MEAN) = HGF_S(node, F_EXPECTED_MEAN) + gain;
 }
@@ -557,7 +594,7 @@ template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const Step<
   const T vope = pi_hat / HGF_S(node, F_PRECISION) + pi_hat * (delta * delta) - B(1);
   HGF_S(node, F_VALUE_PREDICTION_ERROR) = delta;
   HGF_S(node, F_VOLATILITY_PREDICTION_ERROR) = vope;
-  const T cap = T(static_cast<B>(a.max_posterior_precision()));
+  const B cap = static_cast<B>(a.max_posterior_precision());
   const int vu = a.vol_updates();
   if (vu == VU_UNBOUNDED) {
     VolatilityChild<T> c;
@@ -567,7 +604,7 @@ template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const Step<
     c.expected_mean = HGF_S(node, F_EXPECTED_MEAN);
     c.expected_precision = pi_hat;
     T pi, mu;
-    unbounded_mixture<false>(st, c, HGF_S(node, F_EXPECTED_MEAN_VOL), HGF_S(node, F_EXPECTED_PRECISION_VOL), T(B(1)), T(B(0)),
+    unbounded_mixture<false>(st, c, HGF_S(node, F_EXPECTED_MEAN_VOL), HGF_S(node, F_EXPECTED_PRECISION_VOL), B(1), T(B(0)),
                              pi, mu);
     HGF_S(node, F_PRECISION_VOL) = x_min(pi, cap);
     HGF_S(node, F_MEAN_VOL) = mu;
@@ -581,7 +618,7 @@ template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const Step<
     const T gamma_rep = omega * pi_rep;
     const T weight = (omega - prev_var) * pi_rep;
     const T vope_rep = (B(1) / HGF_S(node, F_PRECISION) + delta * delta) * pi_rep - B(1);
-    const T inc = x_max(T(B(0)), B(0.5) * gamma_rep * (gamma_rep + weight * vope_rep));
+    const T inc = x_max(B(0), B(0.5) * gamma_rep * (gamma_rep + weight * vope_rep));
     HGF_S(node, F_PRECISION_VOL) = x_min(HGF_S(node, F_EXPECTED_PRECISION_VOL) + inc, cap);
   } else {
     const T gamma = HGF_S(node, F_EFFECTIVE_PRECISION);
@@ -623,7 +660,7 @@ template <class T, class A> HGF_D void apply_op(const A& a, T* s, const Step<T>&
 // ===========================================================================
 template <class T> HGF_D T binary_surprise(bool x_is_one, const T& mu_hat) {
   using B = base_t<T>;
-  const T m = x_clip(mu_hat, T(static_cast<B>(1e-6)), T(static_cast<B>(1.0 - 1e-6)));
+  const T m = x_clip(mu_hat, static_cast<B>(1e-6), static_cast<B>(1.0 - 1e-6));
   return x_is_one ? -x_log(m) : -x_log(B(1) - m);
 }
 

@@ -154,16 +154,16 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
   for (int t = 0; t < T_steps; ++t) {
     Step<T> st;
     if constexpr (UNIT_DT) {
-      st.dt = T(B(1));
-      st.log_dt = T(B(0));
+      st.dt = B(1);
+      st.log_dt = B(0);
     } else {
-      st.dt = T(time_steps ? HGF_LDG(time_steps + t) : B(1));
+      st.dt = time_steps ? HGF_LDG(time_steps + t) : B(1);
       st.log_dt = x_log(st.dt);
     }
     // prediction sequence (parents before children)
     [[maybe_unused]] int pred_lo = 0, pred_hi = a.n_pred(), upd_lo = 0, upd_hi = a.n_upd();
     if constexpr (Topo::is_static) {
-      a.run_predictions(s, st);
+      a.run_predictions(a, s, st);
     } else {
       // a switching plan (input_custom_sequence, network.py:746-758) picks this step's branch; lax.switch clamps
       if (args.branch_idx) {
@@ -200,7 +200,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
     }
     // prediction errors and posterior updates (children before parents)
     if constexpr (Topo::is_static) {
-      a.run_updates(s, st);
+      a.run_updates(a, s, st);
     } else {
       for (int i = upd_lo; i < upd_hi; ++i) apply_op(a, s, st, a.upd_op(i), a.upd_node(i));
     }

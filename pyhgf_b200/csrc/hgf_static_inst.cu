@@ -9,4 +9,9 @@ namespace hgf {
 using Scalar = Dual<HGF_BASE, HGF_NTAN>;  // 0 tangents: the plain filter
 template cudaError_t launch_one<Scalar, HGF_TOPO_TYPE, HGF_TOPO_TYPE::kSlots, HGF_NRESP>(const Program&, const CallLists&, const ScanArgs&,
                                                                              cudaStream_t);
+#if HGF_NTAN > 0
+// the flavour for calls that differentiate no structural attribute (hgf_ops.cuh::attr, launch_scan picks it)
+template cudaError_t launch_one<Scalar, ConstAttributes<HGF_TOPO_TYPE>, HGF_TOPO_TYPE::kSlots, HGF_NRESP>(const Program&, const CallLists&,
+                                                                                              const ScanArgs&, cudaStream_t);
+#endif
 }

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(lib):
     L = lib.lib()
     for name in declared:
         assert hasattr(L, name), name
-    assert L.hgf_abi_version() == 4
+    assert L.hgf_abi_version() == 5
     assert lib.launch_count() == 0
 
 

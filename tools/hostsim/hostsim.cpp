@@ -34,6 +34,11 @@ extern "C" void sim_binary3_grad(int n, int T, int group, const float* u, const 
                                  const float* params, float* logp, float* grad) {
   run<Topo_binary3, 2, 1>(n, T, group, u, y, attrs, 3, slots, params, RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE, logp, grad);
 }
+// the ConstAttributes<> flavour of the same kernel (no structural attribute is differentiated)
+extern "C" void sim_binary3_grad_const(int n, int T, int group, const float* u, const float* y, const float* attrs, const int* slots,
+                                       const float* params, float* logp, float* grad) {
+  run<ConstAttributes<Topo_binary3>, 2, 1>(n, T, group, u, y, attrs, 3, slots, params, RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE, logp, grad);
+}
 extern "C" void sim_binary3(int n, int T, int group, const float* u, const float* y, const float* attrs, const int* slots,
                             const float* params, int response_fn, float* logp) {
   run<Topo_binary3, 0, 0>(n, T, group, u, y, attrs, 3, slots, params, response_fn, logp, nullptr);

@@ -59,12 +59,12 @@ class Box:
         self.want, self.want_g = o32.batch_grad(self.u.astype(np.float64), os_, self.p.astype(np.float64), "binary_softmax_inverse_temperature",
                                                 resp_inputs=self.y.astype(np.float64), group_size=group, dtype=32)
 
-    def run(self, lib):
+    def run(self, lib, entry="sim_binary3_grad"):
         n = self.p.shape[1]
         T = self.u.shape[-1]
         logp = np.zeros(n, dtype=np.float32)
         grad = np.zeros((3, n), dtype=np.float32)
-        lib.sim_binary3_grad(n, T, self.group, fp(self.u), fp(self.y), fp(self.attrs), fp(self.slots), fp(self.p), fp(logp), fp(grad))
+        getattr(lib, entry)(n, T, self.group, fp(self.u), fp(self.y), fp(self.attrs), fp(self.slots), fp(self.p), fp(logp), fp(grad))
         return logp.astype(np.float64), grad.astype(np.float64)
 
 
