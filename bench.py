@@ -153,7 +153,7 @@ class Workload:
             self.mufu_per_step, self.kernel_kind = MUFU["continuous3_fwd"], "forward logp"
         elif config == 5:
             self.build, self.n_nodes, self.scaling, self.evals_per_step = net_ghgf16, 16, "weak", 2
-            n, T = max(64, int(round(32768 * scale))), 2000
+            n, T = max(64, int(round(32768 * scale))), int(os.environ.get("HGF_BENCH_C5_STEPS", "2000"))  # (the override: short ncu captures)
             rng = np.random.default_rng(1 + rank)
             self.series = ar1_series(T)
             self.keys = [(i, "tonic_volatility") for i in range(4, 12)] + [(i, "tonic_volatility_vol") for i in range(12, 16)]

@@ -403,14 +403,18 @@ template <class B> __global__ void fused_wait_kernel(void* workspace, int G, int
 }
 
 // Occupancy: BASELINE config 4 gives each GPU 65 536 instances = 13.8 warps per SM; the float32 register-
-// resident kernels are bounded to 7 resident 64-thread blocks (<= 144 registers) so that the whole batch
-// is co-resident in one wave instead of 1.7 (a second, mostly empty wave costs ~40 %).
+// resident kernels of the small topologies are bounded to 7 resident 64-thread blocks (<= 144 registers) so that the
+// whole batch is co-resident in one wave instead of 1.7 (a second, mostly empty wave costs ~40 %).  Topologies of up to
+// 8 nodes are bounded to 8 blocks (128 registers, no spills: ptxas -v): BASELINE config 5's 16-node network runs as its two
+// 8-node components on two streams (Network.batch), 2 x 512 blocks for 32 768 instances, and at the 151 registers the
+// compiler takes unbounded only 6 blocks fit an SM -- 888 slots for 1 024 blocks, i.e. a second wave that made the two
+// launches take as long as one after the other (profiles/r2_ncu_counters.json: 0.755 ms each alone, 1.45 ms together).
 #ifndef HGF_WIDE_MIN_BLOCKS
-#define HGF_WIDE_MIN_BLOCKS 1  // resident 64-thread blocks per SM asked of the wide (> 4 nodes) float32 specialisations
+#define HGF_WIDE_MIN_BLOCKS 1  // resident 64-thread blocks per SM asked of the wide (> 8 nodes) float32 specialisations
 #endif
 template <class T, class Topo> constexpr int scan_min_blocks() {
   if constexpr (!Topo::is_static) return 1; else
-  return (sizeof(base_t<T>) == 4 && Topo::kNodes <= 4) ? 7 : (sizeof(base_t<T>) == 4 ? HGF_WIDE_MIN_BLOCKS : 1);
+  return sizeof(base_t<T>) != 4 ? 1 : (Topo::kNodes <= 4 ? 7 : (Topo::kNodes <= 8 ? 8 : HGF_WIDE_MIN_BLOCKS));
 }
 
 template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT, bool REC>

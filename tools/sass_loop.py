@@ -13,12 +13,16 @@ for line in sys.stdin:
         cur[1].append((int(m.group(1), 16), m.group(2)))
 for name, ins in funcs:
     if flt not in name: continue
-    best = None
+    # the time loop: the backward branch whose body holds the most SFU instructions (ties: the longest) -- the
+    # parameter-loading prologue of a wide topology is a longer loop, but has none
+    best, best_key = None, None
     for addr, text in ins:
         m = re.search(r"BRA\S*\s+(?:.*\s)?0x([0-9a-f]+)", text)
         if m:
             tgt = int(m.group(1), 16)
-            if tgt < addr and (best is None or addr - tgt > best[1] - best[0]): best = (tgt, addr)
+            if tgt < addr:
+                key = (sum(1 for a, t in ins if tgt <= a <= addr and "MUFU" in t), addr - tgt)
+                if best is None or key > best_key: best, best_key = (tgt, addr), key
     if not best:
         print(name, "no loop found", len(ins)); continue
     body = [t for a, t in ins if best[0] <= a <= best[1]]
