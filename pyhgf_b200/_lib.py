@@ -107,6 +107,7 @@ class Call(C.Structure):
         ("generative", C.c_int32),
         ("seed", C.c_uint64),
         ("branch_idx", C.c_void_p),
+        ("gradient_mode", C.c_int32),
     ]
 
 

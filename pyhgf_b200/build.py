@@ -65,6 +65,11 @@ def jobs():
                 out.append((os.path.join(CSRC, "hgf_static_inst.cu"), os.path.join(OBJ, f"hgf_static_{topo}_{base}_d{ntan}r{nresp}.o"),
                             [f"-DHGF_TOPO_HEADER=<generated/topo_{topo}.h>", f"-DHGF_TOPO_TYPE=Topo_{topo}",
                              f"-DHGF_BASE={base}", f"-DHGF_NTAN={ntan}", f"-DHGF_NRESP={nresp}"] + os.environ.get("HGF_EXTRA_STATIC_FLAGS", "").split()))
+        rev = os.path.join(gen, "reverse.txt")
+        if os.path.exists(rev):
+            for name in open(rev).read().split():
+                out.append((os.path.join(CSRC, "hgf_reverse_inst.cu"), os.path.join(OBJ, f"hgf_reverse_{name}.o"),
+                            [f"-DHGF_REV_HEADER=<generated/reverse_{name}.h>", f"-DHGF_REV_TYPE=Rev_{name}", f"-DHGF_REV_FN=reverse_{name}"]))
     return out
 
 

@@ -233,13 +233,22 @@ def _write_if_changed(path, text):
 
 def main():
     os.makedirs(GEN, exist_ok=True)
+    from . import revgen
+
     includes, table, manifest = [], [], ["# topology base PF PR  (one translation unit each; written by codegen.py)\n"]
+    reverse = []
     for name, spec in TOPOLOGIES.items():
         _write_if_changed(os.path.join(GEN, f"topo_{name}.h"), generate_topology(name, spec))
         includes.append(f"#include <generated/topo_{name}.h>\n")
         m32 = sum(1 << (pf + 5 * pr) for pf, pr in spec[3])
         m64 = sum(1 << (pf + 5 * pr) for pf, pr in spec[4])
-        table.append(f"HGF_STATIC_TOPO({name}, {m32}u, {m64}u)\n")
+        try:  # the reverse sweep of the topology, where the generator covers its node kinds (revgen.py)
+            _write_if_changed(os.path.join(GEN, f"reverse_{name}.h"), revgen.generate(name, spec[0](), spec[1], spec[2]))
+            reverse.append(name)
+            rev = f"kReverse_{name}"
+        except revgen.Unsupported:
+            rev = "nullptr"
+        table.append(f"HGF_STATIC_TOPO({name}, {m32}u, {m64}u, {rev})\n")
         for pf, pr in spec[3]:
             manifest.append(f"{name} float {pf} {pr}\n")
         for pf, pr in spec[4]:
@@ -247,7 +256,10 @@ def main():
     _write_if_changed(os.path.join(GEN, "static_includes.inc"), "".join(includes))
     _write_if_changed(os.path.join(GEN, "static_table.inc"), "".join(table))
     _write_if_changed(os.path.join(GEN, "instances.txt"), "".join(manifest))
-    keep = {f"topo_{n}.h" for n in TOPOLOGIES} | {"static_includes.inc", "static_table.inc", "instances.txt"}
+    _write_if_changed(os.path.join(GEN, "reverse_table.inc"), "".join(f"HGF_STATIC_REVERSE({n})\n" for n in reverse))
+    _write_if_changed(os.path.join(GEN, "reverse.txt"), "".join(f"{n}\n" for n in reverse))
+    keep = ({f"topo_{n}.h" for n in TOPOLOGIES} | {f"reverse_{n}.h" for n in reverse} |
+            {"static_includes.inc", "static_table.inc", "instances.txt", "reverse_table.inc", "reverse.txt"})
     for f in os.listdir(GEN):
         if f not in keep:
             os.remove(os.path.join(GEN, f))

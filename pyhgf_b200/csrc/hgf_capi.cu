@@ -41,6 +41,9 @@ void count_launches(int n) { g_launches += n; }
 int report_error(const char* msg) { return fail("%s", msg); }
 }  // namespace hgf
 
+// gradient_mode auto: parameters from which the reverse sweep is taken (measured crossover: DESIGN.md §3.1)
+constexpr int kReverseFromParams = 13;
+
 struct hgf_plan {
   Program prog;
   const KernelVariant* variant;
@@ -343,6 +346,22 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
   }
   if (a.trajectories && lists.n_rec > 0) encode_trajectory_map(a, lists.n_rec, c->dtype == 32 ? 4 : 8);
   int n_launched = 0;
+  // the reverse sweep (hgf_call_t::gradient_mode): a plain logp + gradient call on a topology that has one
+  if (want_grad && c->gradient_mode != 1) {
+    const bool plain = !c->trajectories && !c->surprise_pointwise && !c->last_attributes && c->world_size <= 1 && !c->generative &&
+                       !plan->prog.n_branches && c->response_fn != RESP_NONE && c->response_fn != RESP_TOTAL_GAUSSIAN;
+    const bool available = plan->variant->reverse != nullptr && plain;
+    if (c->gradient_mode == 2 && !available)
+      return fail("gradient_mode = reverse: %s", plan->variant->reverse ? "the call asks for outputs only the forward-mode kernels produce"
+                                                                          : "this plan's topology has no generated reverse sweep");
+    if (available && (c->gradient_mode == 2 || c->n_params >= kReverseFromParams)) {
+      lists.n_filter = lists.n_params;
+      const cudaError_t rerr = plan->variant->reverse(plan->prog, lists, a, c->dtype, stream, &n_launched);
+      g_launches += n_launched;
+      if (rerr != cudaSuccess) return fail("reverse sweep launch failed: %s", cudaGetErrorString(rerr));
+      return 0;
+    }
+  }
   cudaError_t err = run_variant(*plan->variant, plan->prog, lists, a, c->dtype, want_grad, stream, &n_launched);
   g_launches += n_launched;
   if (err != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(err));

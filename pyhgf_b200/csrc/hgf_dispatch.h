@@ -11,10 +11,15 @@ namespace hgf {
 using RunFn = cudaError_t (*)(const Program&, const CallLists&, const ScanArgs&, int dtype, bool want_grad, cudaStream_t,
                               int* n_launched);
 
+// The generated reverse sweep of a topology (hgf_reverse.cuh), when there is one: logp + gradient of a plain call
+// (per-instance sums, optional group reduction; no trajectories / pointwise output / fused cross-GPU reduction).
+using ReverseFn = cudaError_t (*)(const Program&, const CallLists&, const ScanArgs&, int dtype, cudaStream_t, int* n_launched);
+
 struct KernelVariant {
   const char* name;
   bool (*matches)(const Program&);  // nullptr: accepts every program
   RunFn run;
+  ReverseFn reverse = nullptr;
 };
 
 // hgf_interp.cu

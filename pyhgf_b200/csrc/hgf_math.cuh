@@ -231,6 +231,14 @@ HGF_HD float exact_rcp(float x) {
 #endif
 }
 HGF_HD double exact_rcp(double x) { return 1.0 / x; }
+HGF_HD float exact_quot(float a, float b) {
+#if HGF_DIV_MODE == 2
+  return a / b;
+#else
+  return exact_div_from_rcp(a, b, sfu_rcp(b));
+#endif
+}
+HGF_HD double exact_quot(double a, double b) { return a / b; }
 
 HGF_HD float pv(float x) { return x; }
 HGF_HD double pv(double x) { return x; }

@@ -758,6 +758,8 @@ class Network:
         if want_grad:
             grad = torch.empty((P, N), device=dev, dtype=dt)
             call.gradient = grad.data_ptr()
+            # "forward" / "reverse" force one of the two gradient kernels (hgf_call_t::gradient_mode); True: the library's choice
+            call.gradient_mode = {"forward": 1, "reverse": 2}.get(want_grad, 0) if isinstance(want_grad, str) else 0
         if n_groups:
             if fused_reduce is not None:
                 if fused_reduce.n_groups != n_groups or fused_reduce.bits != self.bits:
@@ -1374,7 +1376,9 @@ class Network:
             ``input_group_size = g`` a stack ``(G, T[, n_inputs])`` where instance n reads series ``n // g``.
         response_function : one of ``pyhgf_b200.response``'s functions (or its name): fused into the time loop.
         record : ``[(node, attribute), ...]`` leaves to record at every step -> ``result.trajectories``.
-        gradient : also return d(surprise)/d(parameters) (``hgf_logp_grad``).
+        gradient : also return d(surprise)/d(parameters) (``hgf_logp_grad``).  ``True`` lets the library pick between
+            forward-mode tangents in the filter's registers and the checkpointed reverse sweep (taken from 13 parameters
+            on, where the topology has a generated one); ``"forward"`` / ``"reverse"`` force one.
         group / n_groups : sum ``out_scale * surprise`` of the instances of each group (e.g. chain) on the device.
         fused_reduce : a ``pyhgf_b200.distributed.FusedReduce``: the group sums are all-reduced over the ranks
             by the kernel itself (NVLink peer memory); ``result.reduced`` then holds the sums over all ranks.

@@ -354,6 +354,88 @@ def test_gradient_matches_dual_oracle(G, R, datasets, dtype, rtol):
         assert np.median(rel) < 1e-4, (k, np.median(rel))
 
 
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+def test_reverse_sweep_matches_dual_oracle(G, R, datasets, dtype):
+    """The generated checkpointed reverse sweep (csrc/hgf_reverse.cuh, pyhgf_b200/revgen.py; the reference: jax.grad over the
+    scan, pyhgf/model/network.py:612-624) against the forward-mode Dual oracle: 8 parameters of the 3-level binary HGF --
+    volatilities, inverse temperature, initial beliefs, drift, autoconnection -- and 6 of the 4-node continuous HGF
+    including a volatility coupling.  float64 to 1e-7; float32 per instance to the stated 1e-4 / the oracle's sensitivity."""
+    u, y, x = datasets["u"], datasets["y"], datasets["x"][:300]
+    n = 96
+    cases = [
+        (nets.binary3, u, y, "binary_softmax_inverse_temperature", R.binary_softmax_inverse_temperature,
+         [(1, "tonic_volatility"), (2, "tonic_volatility"), ("response_parameter", 0), (1, "mean"), (2, "precision"), (1, "tonic_drift"),
+          (2, "autoconnection_strength"), (1, "precision")],
+         [_grid(n, -6, -3.5, 1), _grid(n, -6, -3.5, 2), np.exp(_grid(n, -0.3, 0.8, 3)), _grid(n, -0.5, 0.5, 4), np.exp(_grid(n, -0.5, 0.5, 5)),
+          _grid(n, -0.01, 0.01, 6), _grid(n, 0.9, 1.0, 7), np.exp(_grid(n, -0.5, 0.5, 8))]),
+        (nets.continuous3, x, None, "first_level_gaussian_surprise", R.first_level_gaussian_surprise,
+         [(1, "tonic_volatility"), (2, "tonic_volatility"), (3, "tonic_volatility"), (2, "volatility_coupling_children", 0),
+          (1, "volatility_coupling_parents", 0), (2, "tonic_drift")],
+         [_grid(n, -12, -9, 1), _grid(n, -3, -1, 2), _grid(n, -3, -1, 3), _grid(n, 0.8, 1.2, 4), _grid(n, 0.8, 1.2, 5), _grid(n, -0.01, 0.01, 6)]),
+    ]
+    for build, data, resp_in, rname, rfn, keys, vals in cases:
+        p = np.stack(vals)
+        if dtype == "float32":
+            p = p.astype(np.float32).astype(np.float64)
+        kw = {} if resp_in is None else {"response_function_inputs": resp_in}
+        res = build(G.Network, dtype=dtype).batch(data, dict(zip(keys, p)), response_function=rfn, gradient="reverse", **kw)
+        fwd = build(G.Network, dtype=dtype).batch(data, dict(zip(keys, p)), response_function=rfn, gradient="forward", **kw)
+        o = build(onet.Network, dtype=dtype).create_belief_propagation_fn()
+        slots = [o.slot(-1, "response_parameter", k[1]) if k[0] == "response_parameter" else o.slot(*k) for k in keys]
+
+        def oracle(q):
+            s_, g_ = o.batch_grad(data, slots, q, rname, resp_inputs=resp_in, dtype=32 if dtype == "float32" else 64)
+            return np.concatenate([s_[None], g_])
+
+        if dtype == "float64":
+            want = oracle(p)
+            assert np.allclose(res.surprise.cpu().numpy(), want[0], rtol=1e-9)
+            for i, k in enumerate(keys):
+                got = res.gradient[k].cpu().numpy()
+                assert np.allclose(got, want[1 + i], rtol=1e-7, atol=1e-7 * np.abs(want[1 + i]).max()), (build.__name__, k)
+                assert np.allclose(got, fwd.gradient[k].cpu().numpy(), rtol=1e-7, atol=1e-7 * np.abs(want[1 + i]).max())
+            continue
+        scales = np.abs(oracle(p)[1:]).max(axis=1)
+        floor = np.concatenate([[0.0 if resp_in is not None else 100.0], RTOL_SUM * scales])[:, None]
+        filt = [i for i, k in enumerate(keys) if k[0] != "response_parameter"]
+        want, sens = conditioning.sensitivity(oracle, p, rows=filt, n_draws=16, floor=floor)
+        assert_conditioned(res.surprise.double().cpu().numpy(), want[0], sens[0], RTOL_SUM, floor=float(floor[0, 0]), what="logp (reverse)")
+        for i, k in enumerate(keys):
+            assert_conditioned(res.gradient[k].double().cpu().numpy(), want[1 + i], sens[1 + i], RTOL_SUM, amplification=AMPLIFICATION_GRAD,
+                               floor=RTOL_SUM * scales[i], what=(build.__name__, k))
+
+
+def test_reverse_sweep_dispatch(G, R, datasets):
+    """gradient=True takes the reverse sweep from 13 parameters on (one launch instead of three forward-mode passes) and the
+    two kernels agree; asking for it where it cannot run is an error, not a silent fallback."""
+    from pyhgf_b200 import _lib
+
+    u, y = datasets["u"], datasets["y"]
+    n = 64
+    keys = [(1, "tonic_volatility"), (2, "tonic_volatility"), ("response_parameter", 0), (1, "mean"), (2, "mean"), (1, "precision"), (2, "precision"),
+            (1, "tonic_drift"), (2, "tonic_drift"), (2, "autoconnection_strength"), (1, "autoconnection_strength"),
+            (2, "volatility_coupling_children", 0), (1, "volatility_coupling_parents", 0)]
+    vals = [_grid(n, -6, -3.5, 1), _grid(n, -6, -3.5, 2), np.exp(_grid(n, -0.3, 0.8, 3)), _grid(n, -0.5, 0.5, 4), _grid(n, -0.5, 0.5, 5),
+            np.exp(_grid(n, -0.5, 0.5, 6)), np.exp(_grid(n, -0.5, 0.5, 7)), _grid(n, -0.01, 0.01, 8), _grid(n, -0.01, 0.01, 9), _grid(n, 0.9, 1.0, 10),
+            _grid(n, 0.9, 1.0, 11), _grid(n, 0.8, 1.2, 12), _grid(n, 0.8, 1.2, 13)]
+    kw = dict(response_function=R.binary_softmax_inverse_temperature, response_function_inputs=y)
+    net = nets.binary3(G.Network, dtype="float64")
+    before = _lib.launch_count()
+    auto = net.batch(u, dict(zip(keys, vals)), gradient=True, **kw)
+    assert _lib.launch_count() - before == 1          # the reverse sweep: one kernel
+    before = _lib.launch_count()
+    fwd = net.batch(u, dict(zip(keys, vals)), gradient="forward", **kw)
+    assert _lib.launch_count() - before == 3          # 12 filter parameters + 1 response parameter: three forward-mode passes
+    for k in keys:
+        a, b = auto.gradient[k].cpu().numpy(), fwd.gradient[k].cpu().numpy()
+        assert np.allclose(a, b, rtol=1e-7, atol=1e-7 * np.abs(b).max()), k
+    with pytest.raises(_lib.BackendError, match="reverse"):
+        net.batch(u, dict(zip(keys[:3], vals[:3])), gradient="reverse", record=[(1, "mean")], **kw)
+    with pytest.raises(_lib.BackendError, match="no generated reverse sweep"):
+        nets.volatile2(G.Network).batch(datasets["x"][:50], {(1, "tonic_volatility_vol"): np.full(4, -3.0)},
+                                        response_function=R.first_level_gaussian_surprise, gradient="reverse")
+
+
 def test_gradient_continuous_and_coupling(G, R, datasets):
     x = datasets["x"][:300]
     n = 64

@@ -8,6 +8,10 @@
 #include "hgf_scan.cuh"
 #include <generated/topo_binary3.h>
 #include <generated/topo_continuous3.h>
+#include "hgf_reverse.cuh"
+#include <generated/reverse_binary3.h>
+#include <generated/reverse_continuous3.h>
+#include <vector>
 
 using namespace hgf;
 
@@ -38,6 +42,37 @@ extern "C" void sim_binary3_grad(int n, int T, int group, const float* u, const 
 extern "C" void sim_binary3_grad_const(int n, int T, int group, const float* u, const float* y, const float* attrs, const int* slots,
                                        const float* params, float* logp, float* grad) {
   run<ConstAttributes<Topo_binary3>, 2, 1>(n, T, group, u, y, attrs, 3, slots, params, RESP_BINARY_SOFTMAX_INVERSE_TEMPERATURE, logp, grad);
+}
+// the generated reverse sweep (hgf_reverse.cuh) of the same evaluation; params are ALL per-instance parameters [P][n]
+template <class F, class Rev>
+static void run_reverse(int n_inst, int n_steps, int group, const F* u, const F* y, const F* attrs, int n_params, const int* slots, const F* params,
+                        int response_fn, F* logp, F* grad) {
+  Program prog{};
+  prog.max_posterior_precision = 1e10;
+  CallLists lists{};
+  lists.n_params = n_params;
+  lists.n_filter = n_params;
+  for (int q = 0; q < n_params; ++q) { lists.param_slot[q] = static_cast<uint16_t>(slots[q]); lists.param_row[q] = static_cast<uint16_t>(q); }
+  ScanArgs a{};
+  a.n_instances = n_inst; a.ld = n_inst; a.n_steps = n_steps;
+  a.input_group_size = group; a.response_group_size = group;
+  a.input_data = u; a.response_inputs = y; a.attributes = attrs; a.params = params;
+  a.surprise_sum = logp; a.gradient = grad; a.out_scale = 1.0; a.response_fn = response_fn;
+  std::vector<F> state(static_cast<size_t>(n_steps) * Rev::kCarried * n_inst);
+#pragma omp parallel for schedule(dynamic, 64)
+  for (int i = 0; i < n_inst; ++i) reverse_instance<F, Rev, true>(prog, lists, a, i, true, state.data());
+}
+extern "C" void sim_binary3_reverse(int n, int T, int group, const float* u, const float* y, const float* attrs, int n_params, const int* slots,
+                                    const float* params, int response_fn, float* logp, float* grad) {
+  run_reverse<float, Rev_binary3<float>>(n, T, group, u, y, attrs, n_params, slots, params, response_fn, logp, grad);
+}
+extern "C" void sim_binary3_reverse_f64(int n, int T, int group, const double* u, const double* y, const double* attrs, int n_params, const int* slots,
+                                        const double* params, int response_fn, double* logp, double* grad) {
+  run_reverse<double, Rev_binary3<double>>(n, T, group, u, y, attrs, n_params, slots, params, response_fn, logp, grad);
+}
+extern "C" void sim_continuous3_reverse_f64(int n, int T, const double* u, const double* attrs, int n_params, const int* slots, const double* params,
+                                            double* logp, double* grad) {
+  run_reverse<double, Rev_continuous3<double>>(n, T, 0, u, nullptr, attrs, n_params, slots, params, RESP_FIRST_LEVEL_GAUSSIAN, logp, grad);
 }
 extern "C" void sim_binary3(int n, int T, int group, const float* u, const float* y, const float* attrs, const int* slots,
                             const float* params, int response_fn, float* logp) {
