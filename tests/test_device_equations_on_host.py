@@ -56,3 +56,49 @@ def test_shipped_policy_with_emulated_sfu_stays_inside_the_parity_bound(box):
     round1, _ = b.run(hostsim.build(["-DHGF_RESP_MODE=0"]))
     err = np.abs(round1 / want - 1)
     assert (err > conditioning.tolerance(sens, 1e-4, 4.0)).sum() > stats["n_over_rtol"] + 2  # what the policy fixes
+
+
+def test_generated_reverse_sweep_is_the_oracles_gradient(box, datasets):
+    """csrc/hgf_reverse.cuh + generated/reverse_*.h (pyhgf_b200/revgen.py) compiled for the host, float64: the summed
+    surprise is the oracle's bit for bit and all eight gradients -- volatilities, inverse temperature, initial beliefs,
+    tonic drift, autoconnection -- are the Dual<double> oracle's to 1e-10; same for the 4-node continuous HGF with a
+    volatility coupling among the parameters."""
+    import ctypes as C
+
+    from pyhgf_b200.network import Network
+
+    hostsim, _ = box
+    lib = hostsim.build(["@"])
+    fp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rng = np.random.default_rng(3)
+    n = 48
+    u, y, x = (np.ascontiguousarray(datasets[k], dtype=np.float64) for k in ("u", "y", "x"))
+    x = np.ascontiguousarray(x[:300])
+    cases = [
+        (nets.binary3, "sim_binary3_reverse_f64", u, y, "binary_softmax_inverse_temperature",
+         [(1, "tonic_volatility"), (2, "tonic_volatility"), ("response_parameter", 0), (1, "mean"), (2, "precision"), (1, "tonic_drift"),
+          (2, "autoconnection_strength"), (1, "precision")],
+         [rng.uniform(-6, -3, n), rng.uniform(-6, -3, n), np.exp(rng.uniform(-0.3, 0.8, n)), rng.uniform(-0.5, 0.5, n), np.exp(rng.uniform(-0.5, 0.5, n)),
+          rng.uniform(-0.01, 0.01, n), rng.uniform(0.9, 1.0, n), np.exp(rng.uniform(-0.5, 0.5, n))]),
+        (nets.continuous3, "sim_continuous3_reverse_f64", x, None, "first_level_gaussian_surprise",
+         [(1, "tonic_volatility"), (2, "tonic_volatility"), (3, "tonic_volatility"), (2, "volatility_coupling_children", 0), (2, "tonic_drift"), (3, "mean")],
+         [rng.uniform(-12, -9, n), rng.uniform(-3, -1, n), rng.uniform(-3, -1, n), rng.uniform(0.8, 1.2, n), rng.uniform(-0.01, 0.01, n), rng.uniform(0.5, 1.5, n)]),
+    ]
+    for build, entry, series, resp, rname, keys, vals in cases:
+        net = build(Network, dtype="float64")
+        net.create_belief_propagation_fn()
+        plan = net._get_plan(1)
+        attrs = np.ascontiguousarray(net._flatten(plan), dtype=np.float64)
+        slots = np.array([net._resolve_slot(plan, k) for k in keys], dtype=np.int32)
+        p = np.ascontiguousarray(np.stack(vals))
+        logp, grad = np.zeros(n), np.zeros((len(keys), n))
+        if resp is not None:
+            getattr(lib, entry)(n, len(series), 0, fp(series), fp(resp), fp(attrs), len(keys), fp(slots), fp(p), 5, fp(logp), fp(grad))
+        else:
+            getattr(lib, entry)(n, len(series), fp(series), fp(attrs), len(keys), fp(slots), fp(p), fp(logp), fp(grad))
+        o = build(onet.Network, dtype="float64").create_belief_propagation_fn()
+        oslots = [o.slot(-1, "response_parameter", k[1]) if k[0] == "response_parameter" else o.slot(*k) for k in keys]
+        want_s, want_g = o.batch_grad(series, oslots, p, rname, resp_inputs=resp)
+        assert np.array_equal(logp, want_s), build.__name__
+        for i, k in enumerate(keys):
+            assert np.allclose(grad[i], want_g[i], rtol=1e-9, atol=1e-10 * np.abs(want_g[i]).max()), (build.__name__, k)

@@ -25,11 +25,14 @@ def build(flags):
     flags = [f for f in flags if f and f != "@"]
     src = os.path.join(ROOT, "tools", "hostsim", "hostsim.cpp")
     h = hashlib.sha1(repr((flags, emulate)).encode())
-    for f in [src] + [os.path.join(ROOT, "pyhgf_b200", "csrc", x) for x in ("hgf_math.cuh", "hgf_ops.cuh", "hgf_scan.cuh", "hgf_program.h")]:
+    csrc = os.path.join(ROOT, "pyhgf_b200", "csrc")
+    deps = [os.path.join(csrc, x) for x in ("hgf_math.cuh", "hgf_ops.cuh", "hgf_scan.cuh", "hgf_program.h", "hgf_reverse.cuh")]
+    deps += sorted(os.path.join(csrc, "generated", x) for x in os.listdir(os.path.join(csrc, "generated")) if x.endswith(".h"))
+    for f in [src] + deps:
         h.update(open(f, "rb").read())
     so = os.path.join(WORK, f"sim_{h.hexdigest()[:12]}.so")
     if not os.path.exists(so):
-        cmd = ["g++", "-O2", "-ffp-contract=off", "-fopenmp", "-shared", "-fPIC", "-Wno-attributes", "-I", os.path.join(ROOT, "pyhgf_b200", "csrc"),
+        cmd = ["g++", "-O2", "-ffp-contract=off", "-fopenmp", "-shared", "-fPIC", "-Wno-attributes", "-Wno-unused-variable", "-I", os.path.join(ROOT, "pyhgf_b200", "csrc"),
                "-I", "/usr/local/cuda/include"] + (["-DHGF_HOST_EMULATE_SFU"] if emulate else []) + flags + [src, "-o", so]
         subprocess.run(cmd, check=True)
     return C.CDLL(so)
