@@ -1322,6 +1322,9 @@ class Network:
                 raise ValueError(f"per-instance parameters disagree on the batch size: {sorted(sizes)}")
             n_instances = sizes.pop() if sizes else (x.shape[0] * input_group_size if grouped else 1)
         dev = self.device
+        fused = self._fused_isomorphic_components(comps, x, obs, parameters, time_steps, n_instances, input_group_size, record, stream)
+        if fused is not None:
+            return fused
         cur = torch.cuda.current_stream(dev) if stream is None else stream
         parts, streams, merged_traj = [], [], {}
         for nodes in comps:
@@ -1357,6 +1360,65 @@ class Network:
         out = ComponentsResult(parts, streams, dev)
         out.trajectories = {tuple(key): merged_traj[(int(key[0]), key[1])] for key in record}
         return out
+
+    def _fused_isomorphic_components(self, comps, x, obs, parameters, time_steps, n_instances, input_group_size, record, stream):
+        """WIDE networks made of ISOMORPHIC components -- the reference's "wide (x10)" benchmark network, ten 3-level binary
+        HGFs side by side (docs/paper.ipynb cell 46, docs/benchmark_results.csv:4), or BASELINE config 5's two 8-node halves
+        -- run as ONE launch of the component's kernel over C x N threads: the components of an instance are C lanes'
+        worth of work instead of one thread's, thread (c, n) carrying component c of instance n (component-major, so that
+        a warp reads ONE component's series: broadcast loads).  Returns None unless every component has the same
+        edges, attributes, recorded leaves and per-instance parameter keys (then the per-component launches below run)."""
+        if os.environ.get("HGF_FUSE_COMPONENTS") == "0":
+            return None
+        inputs = list(self.input_idxs)
+        subs = [self._component_network(nodes) for nodes in comps]
+        sub0, local0 = subs[0]
+        sig = lambda net: (net.edges, [sorted((k, repr(v)) for k, v in net.attributes[i].items()) for i in range(net.n_nodes)], net._input_idxs)  # noqa: E731
+        if any(sig(sub) != sig(sub0) for sub, _ in subs[1:]):
+            return None
+        per_comp_rec, per_comp_par = [], []
+        for sub, local in subs:
+            per_comp_rec.append([(local[int(n)], f) for n, f in record if int(n) in local])
+            pk = {}
+            for key, val in parameters.items():
+                if isinstance(key, str) or key[0] in ("response_parameter", "precision_clipping_value") or key[0] == -1:
+                    return None  # shared / response parameters: the per-component path handles them
+                if int(key[0]) in local:
+                    pk[(local[int(key[0])],) + tuple(key[1:])] = val
+            per_comp_par.append(pk)
+        if any(r != per_comp_rec[0] for r in per_comp_rec[1:]) or any(set(q) != set(per_comp_par[0]) for q in per_comp_par[1:]):
+            return None
+        if not per_comp_rec[0]:
+            return None
+        C, N = len(comps), int(n_instances)
+        grouped = input_group_size > 0
+        if grouped and x.shape[0] * input_group_size != N:
+            return None
+        dev, dt = self.device, _torch_dtype(self.bits)
+        cols = [[c for c, g in enumerate(inputs) if g in local] for _, local in subs]
+        x = x.to(device=dev, dtype=dt)
+        series = torch.cat([x[..., c] if grouped else x[..., c][None] for c in cols], dim=0).contiguous()  # [C or C*G, T, n_fed]
+        mask = None
+        if obs is not None:
+            obs = obs.to(dev)
+            mask = torch.cat([obs[..., c] if grouped else obs[..., c][None] for c in cols], dim=0).contiguous()
+        params = {}
+        for key in per_comp_par[0]:
+            parts = []
+            for pk in per_comp_par:
+                v = torch.as_tensor(np.asarray(pk[key]) if not torch.is_tensor(pk[key]) else pk[key]).to(device=dev, dtype=dt).reshape(-1)
+                parts.append(v.expand(N) if v.numel() == 1 else v)
+            params[key] = torch.cat(parts)
+        r = sub0.batch(series, params, time_steps=time_steps, observed=mask, n_instances=C * N, input_group_size=input_group_size if grouped else N,
+                       record=per_comp_rec[0], stream=stream)
+        traj = {}
+        for c, (_, local) in enumerate(subs):
+            back = {v: g for g, v in local.items()}
+            for (n_loc, f), t in r.trajectories.items():
+                traj[(back[n_loc], f)] = t[c * N:(c + 1) * N]
+        r.trajectories = {tuple(key): traj[(int(key[0]), key[1])] for key in record}
+        r.kernel_name = f"components({C}) in one launch: {r.kernel_name}"
+        return r
 
     def batch(self, input_data, parameters: Optional[dict] = None, *, response_function=None,
               response_function_inputs=None, response_function_parameters=None, time_steps=None, observed=None,

@@ -1022,19 +1022,57 @@ def test_disconnected_network_is_split_over_components(G, monkeypatch):
     record = [(i, k) for i in range(16) for k in nets.BELIEFS + (("mean_vol", "precision_vol") if i >= 12 else ())]
     obs = (rng.uniform(size=x.shape) > 0.05).astype(np.uint8)
     out = {}
-    for flag in ("1", "0"):
-        monkeypatch.setenv("HGF_SPLIT_COMPONENTS", flag)
+    for name, split, fuse in (("fused", "1", "1"), ("streams", "1", "0"), ("single", "0", "1")):
+        monkeypatch.setenv("HGF_SPLIT_COMPONENTS", split)
+        monkeypatch.setenv("HGF_FUSE_COMPONENTS", fuse)
         res = nets.ghgf16(G.Network).batch(x, params, record=record, observed=obs, time_steps=np.full(300, 0.5))
         res.relaunch()
         torch.cuda.synchronize()
-        out[flag] = res
-    assert out["1"].kernel_name == "components(2): static:ghgf8 | static:ghgf8" and out["0"].kernel_name == "static:ghgf16"
+        out[name] = res
+    # the two halves are isomorphic: ONE launch of the 8-node kernel over 2 x 700 threads; with fusing off, one launch per
+    # component on its own stream; with splitting off, the 16-node kernel
+    assert out["fused"].kernel_name == "components(2) in one launch: static:ghgf8"
+    assert out["streams"].kernel_name == "components(2): static:ghgf8 | static:ghgf8" and out["single"].kernel_name == "static:ghgf16"
     for k in record:
-        a, b = out["1"].trajectories[k], out["0"].trajectories[k]
-        assert a.shape == b.shape == (n, 300)
-        assert torch.allclose(a, b, rtol=1e-6, atol=1e-7, equal_nan=True), k
+        a, b, c = out["fused"].trajectories[k], out["single"].trajectories[k], out["streams"].trajectories[k]
+        assert a.shape == b.shape == c.shape == (n, 300)
+        assert torch.equal(torch.nan_to_num(a), torch.nan_to_num(c)), k   # the same kernel, launched once or per component
+        # the 8-node and the 16-node kernel are two float32 evaluations in different instruction order (missing observations,
+        # dt = 0.5, 300 steps): held to 1e-4 here; each is held to 1e-5 against the oracle in test_config5_trajectories_layout
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-5, equal_nan=True), k
     # a connected network, a call with a response function or a gradient are not split
     assert nets.binary3(G.Network).connected_components() == [[0, 1, 2]]
+
+
+def test_wide_x10_network_runs_as_one_launch_of_the_component_kernel(G, datasets):
+    """The reference's "wide (x10)" benchmark network (docs/paper.ipynb cell 46: ten 3-level binary HGFs side by side, 30
+    nodes, each fed its own input column): the ten components of every instance run as 10 x N threads of the
+    register-resident 3-level kernel in one launch, and every component's trajectories are the single 3-level network's."""
+    import torch
+
+    u = datasets["u"]
+    wide = G.Network()
+    for i in range(10):
+        wide.add_nodes(kind="binary-state").add_nodes(value_children=3 * i).add_nodes(volatility_children=3 * i + 1)
+    n = 40
+    rng = np.random.default_rng(9)
+    series = np.stack([np.roll(u, 7 * i) for i in range(10)], axis=1)  # a different column per component
+    params = {(3 * i + 1, "tonic_volatility"): rng.uniform(-6, -3.5, n) for i in range(10)}
+    params.update({(3 * i + 2, "tonic_volatility"): rng.uniform(-6, -3.5, n) for i in range(10)})
+    record = [(j, k) for j in range(30) for k in ("mean", "expected_mean")]
+    res = wide.batch(series, params, record=record)
+    assert res.kernel_name == "components(10) in one launch: static:binary3"
+    for i in (0, 4, 9):
+        one = nets.binary3(G.Network).batch(series[:, i], {(1, "tonic_volatility"): params[(3 * i + 1, "tonic_volatility")],
+                                                            (2, "tonic_volatility"): params[(3 * i + 2, "tonic_volatility")]},
+                                            record=[(j, k) for j in range(3) for k in ("mean", "expected_mean")])
+        for j in range(3):
+            for k in ("mean", "expected_mean"):
+                assert torch.equal(torch.nan_to_num(res.trajectories[(3 * i + j, k)]), torch.nan_to_num(one.trajectories[(j, k)])), (i, j, k)
+    o = nets.binary3(onet.Network, om2=float(np.float32(params[(13, "tonic_volatility")][5])), om3=float(np.float32(params[(14, "tonic_volatility")][5])))
+    o.input_data(series[:, 4])
+    got = res.trajectories[(13, "mean")][5].double().cpu().numpy()
+    assert np.allclose(got, o.node_trajectories[1]["mean"], rtol=RTOL_TRAJ, atol=1e-6)
 
 
 # ---------------------------------------------------------------- ef-state nodes (hgf_ef_filter)
