@@ -406,7 +406,7 @@ def test_reverse_sweep_matches_dual_oracle(G, R, datasets, dtype):
 
 
 def test_reverse_sweep_dispatch(G, R, datasets):
-    """gradient=True takes the reverse sweep from 13 parameters on (one launch instead of three forward-mode passes) and the
+    """gradient=True takes the reverse sweep from 13 parameters on (one launch instead of four forward-mode passes) and the
     two kernels agree; asking for it where it cannot run is an error, not a silent fallback."""
     from pyhgf_b200 import _lib
 
@@ -425,7 +425,7 @@ def test_reverse_sweep_dispatch(G, R, datasets):
     assert _lib.launch_count() - before == 1          # the reverse sweep: one kernel
     before = _lib.launch_count()
     fwd = net.batch(u, dict(zip(keys, vals)), gradient="forward", **kw)
-    assert _lib.launch_count() - before == 3          # 12 filter parameters + 1 response parameter: three forward-mode passes
+    assert _lib.launch_count() - before == 4          # 13 parameters, 4 tangents per float64 pass: four forward-mode passes
     for k in keys:
         a, b = auto.gradient[k].cpu().numpy(), fwd.gradient[k].cpu().numpy()
         assert np.allclose(a, b, rtol=1e-7, atol=1e-7 * np.abs(b).max()), k
