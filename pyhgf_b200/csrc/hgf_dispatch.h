@@ -31,6 +31,9 @@ const KernelVariant* select_variant(const Program& prog);
 // on-demand specialisations (hgf_register_specialisation): consulted before the built-in table
 void register_variant(const KernelVariant* v);
 
+// hgf_select.cu: the library's own stream-ordered memory pool on the current device (the reverse sweep's checkpoints)
+cudaError_t scratch_pool(cudaMemPool_t* out);
+
 inline cudaError_t run_variant(const KernelVariant& v, const Program& prog, const CallLists& lists, const ScanArgs& args, int dtype,
                                bool want_grad, cudaStream_t stream, int* n_launched) {
   return v.run(prog, lists, args, dtype, want_grad, stream, n_launched);

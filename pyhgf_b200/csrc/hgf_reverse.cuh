@@ -12,6 +12,9 @@
 // Cost: ~8.5 forward passes measured (profiles/r2_grad_scaling.log), whatever the number of parameters; the attribute vector, its adjoint and the undo log of one
 // step live in registers (every index is a literal after inlining).
 #pragma once
+#ifdef __CUDACC__
+#include "hgf_dispatch.h"  // scratch_pool
+#endif
 #include "hgf_scan.cuh"
 
 namespace hgf {
@@ -113,8 +116,10 @@ HGF_D F reverse_instance(const Program& prog, const CallLists& lists, const Scan
 }
 
 #ifdef __CUDACC__
+// float32: bounded to 7 resident blocks per SM (128 registers; ptxas spills 30-400 bytes of the undo log) so that 65 536
+// instances are one wave, like the forward-mode kernels (hgf_scan.cuh::scan_min_blocks): 3.8 -> 3.3 ms on config 4's batch
 template <class F, class Rev, bool UNIT_DT>
-__global__ void __launch_bounds__(SCAN_THREADS)
+__global__ void __launch_bounds__(SCAN_THREADS, sizeof(F) == 4 ? 7 : 1)
 reverse_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLists lists, const __grid_constant__ ScanArgs args, F* state) {
   long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool active = n < args.n_instances;
@@ -126,14 +131,18 @@ reverse_kernel(const __grid_constant__ Program prog, const __grid_constant__ Cal
   }
 }
 
-// Launch: the checkpoint array is stream-ordered scratch (cudaMallocAsync / cudaFreeAsync: no synchronisation).
+// Launch: the checkpoint array is stream-ordered scratch from the library's own pool (hgf_select.cu::scratch_pool;
+// cudaMallocFromPoolAsync / cudaFreeAsync: no synchronisation, and the pool keeps the memory between launches).
 template <class F, class Rev>
 cudaError_t launch_reverse(const Program& prog, const CallLists& lists, const ScanArgs& args, cudaStream_t stream) {
   const long long blocks = (args.n_instances + SCAN_THREADS - 1) / SCAN_THREADS;
   if (blocks == 0) return cudaSuccess;
   F* state = nullptr;
   const size_t bytes = static_cast<size_t>(args.n_steps > 0 ? args.n_steps : 1) * Rev::kCarried * static_cast<size_t>(args.ld) * sizeof(F);
-  cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&state), bytes, stream);
+  cudaMemPool_t pool = nullptr;
+  cudaError_t e = scratch_pool(&pool);
+  if (e != cudaSuccess) return e;
+  e = cudaMallocFromPoolAsync(reinterpret_cast<void**>(&state), bytes, pool, stream);
   if (e != cudaSuccess) return e;
   if (args.time_steps) reverse_kernel<F, Rev, false><<<static_cast<unsigned>(blocks), SCAN_THREADS, 0, stream>>>(prog, lists, args, state);
   else reverse_kernel<F, Rev, true><<<static_cast<unsigned>(blocks), SCAN_THREADS, 0, stream>>>(prog, lists, args, state);

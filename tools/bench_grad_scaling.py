@@ -20,8 +20,8 @@ def col(lo, hi, log=False):
     return torch.as_tensor(np.exp(v) if log else v, dtype=torch.float32, device=dev)
 
 
-def time_launch(res, reps=5):
-    for _ in range(2):
+def time_launch(res, reps=7):
+    for _ in range(4):
         res.relaunch()
     torch.cuda.synchronize()
     ts = []
@@ -52,7 +52,7 @@ cases["continuous3"] = dict(
             ((2, "volatility_coupling_children", 0), col(0.8, 1.2)), ((1, "volatility_coupling_parents", 0), col(0.8, 1.2)),
             ((3, "volatility_coupling_children", 0), col(0.8, 1.2)), ((2, "volatility_coupling_parents", 0), col(0.8, 1.2))])
 
-print(f"# {torch.cuda.get_device_name(0)}; N = {N} instances; ms per logp+grad launch (median of 5, inputs resident)")
+print(f"# {torch.cuda.get_device_name(0)}; N = {N} instances; ms per logp+grad launch (median of 7 after 4 warm-up launches, inputs resident)")
 for name, c in cases.items():
     net = c["net"]()
     kw = dict(response_function=c["resp"])
