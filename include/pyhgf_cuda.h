@@ -184,7 +184,23 @@ int hgf_filter(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
 /* Forward filter + d(surprise_sum)/d(params) in the same pass.  Device pointers. */
 int hgf_logp_grad(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
 
-/* Same, with every data pointer in HOST memory (pageable or pinned); copies in, runs, copies out, synchronises.
+/* hgf_logp_grad's reverse sweep (gradient_mode = 2) for callers that cannot allocate: code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc.  (No counterpart in the reference.)
+ * hgf_logp_grad takes the sweep's checkpoint array from cudaMallocAsync; this entry point keeps it in
+ * a static device array of HGF_NOALLOC_SCRATCH_BYTES (32 MiB, held by every GPU that loads the library until the
+ * process exits) and calls no cudaMalloc, cudaFree or allocating library routine.  Scope: the 3-level binary HGF
+ * (hgf_plan_kernel_name() == "static:binary3"), float32, a per-trial response function, outputs surprise_sum /
+ * gradient / reduced; n_steps * n_instances <= HGF_NOALLOC_MAX_STEP_INSTANCES (e.g. 320 trials x 6 553 instances).
+ * Anything else is rejected with an error (hgf_last_error()).  Same inputs, outputs and results as hgf_logp_grad.
+ * The scratch is shared by every call on a device and keeps the last call's contents; nothing in it needs clearing
+ * (a launch reads back only checkpoints it has written itself), but two calls that OVERLAP on the GPU (different
+ * streams) race on it: serialise them.  The first call on each device looks up the array's device address
+ * (cudaGetSymbolAddress); make that call outside stream capture. */
+#define HGF_NOALLOC_SCRATCH_BYTES 33554432
+#define HGF_NOALLOC_MAX_STEP_INSTANCES 2097152
+int hgf_logp_grad_reverse_noalloc(const hgf_plan_t* plan, const hgf_call_t* call, void* stream);
+
+/* hgf_filter / hgf_logp_grad with every data pointer in HOST memory (pageable or pinned); copies in, runs, copies out, synchronises.
  * With a fused cross-GPU reduction (world_size > 1; peer_workspace stays a table of DEVICE addresses) a non-NULL host
  * `reduced` receives the sums over ALL ranks: the call waits for every rank's deposit before copying them out. */
 int hgf_filter_host(const hgf_plan_t* plan, const hgf_call_t* call, int32_t device);

@@ -117,7 +117,7 @@ EXPORTS = (
     "hgf_plan_slot_coupling", "hgf_plan_slot_clipping", "hgf_plan_slot_response", "hgf_plan_kernel_name",
     "hgf_filter", "hgf_logp_grad", "hgf_filter_host", "hgf_logp_grad_host", "hgf_launch_count",
     "hgf_fused_reduce_bytes", "hgf_fused_reduce_result_offset", "hgf_fused_reduce_wait", "hgf_register_specialisation", "hgf_ef_filter",
-    "hgf_categorical_update",
+    "hgf_categorical_update", "hgf_logp_grad_reverse_noalloc",
 )
 
 _lib = None
@@ -193,7 +193,7 @@ def lib() -> C.CDLL:
     L.hgf_plan_slot_response.restype = C.c_int32
     L.hgf_plan_kernel_name.argtypes = [C.c_void_p]
     L.hgf_plan_kernel_name.restype = C.c_char_p
-    for name in ("hgf_filter", "hgf_logp_grad"):
+    for name in ("hgf_filter", "hgf_logp_grad", "hgf_logp_grad_reverse_noalloc"):
         f = getattr(L, name)
         f.argtypes = [C.c_void_p, C.POINTER(Call), C.c_void_p]
         f.restype = C.c_int

@@ -48,7 +48,7 @@ def _headers():
 def jobs():
     """(source, object, extra flags) of every translation unit."""
     out = []
-    for name in ("hgf_capi", "hgf_select", "hgf_interp", "hgf_static", "hgf_ef", "hgf_categorical", "hgf_fused"):
+    for name in ("hgf_capi", "hgf_select", "hgf_interp", "hgf_static", "hgf_ef", "hgf_categorical", "hgf_fused", "hgf_noalloc"):
         out.append((os.path.join(CSRC, name + ".cu"), os.path.join(OBJ, name + ".o"), []))
     for tag, base, ntan in INTERP_SCALARS:
         out.append((os.path.join(CSRC, "hgf_interp_inst.cu"), os.path.join(OBJ, f"hgf_interp_{tag}.o"),

@@ -368,6 +368,41 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
   return 0;
 }
 
+namespace hgf {
+// For hgf_noalloc.cu (hgf_logp_grad_reverse_noalloc): validate a plain logp + gradient call on the plan of the topology
+// `kernel` ("static:binary3") and lower it to the reverse sweep's arguments.  Launches and allocates nothing.
+int lower_reverse_call(const hgf_plan_t* plan, const hgf_call_t* c, const char* kernel, const Program** prog, CallLists* lists, ScanArgs* a) {
+  if (check_call(plan, c, true, *lists)) return 1;
+  if (std::strcmp(plan->variant->name, kernel) != 0)
+    return fail("this entry point runs the '%s' kernel only; the plan dispatches to '%s'", kernel, plan->variant->name);
+  if (c->trajectories || c->surprise_pointwise || c->last_attributes || c->world_size > 1 || c->generative || plan->prog.n_branches ||
+      c->response_fn == RESP_NONE || c->response_fn == RESP_TOTAL_GAUSSIAN)
+    return fail("the reverse sweep returns the summed surprise and its gradient only (no trajectories / pointwise output / fused "
+                "cross-GPU reduction) and needs a per-trial response function");
+  lists->n_filter = lists->n_params;
+  std::memset(a, 0, sizeof *a);
+  a->n_instances = c->n_instances;
+  a->ld = c->n_instances;
+  a->n_steps = c->n_steps;
+  a->input_group_size = c->input_group_size;
+  a->response_group_size = c->response_group_size;
+  a->input_data = c->input_data;
+  a->observed = c->observed;
+  a->time_steps = c->time_steps;
+  a->attributes = c->attributes;
+  a->params = c->params;
+  a->response_inputs = c->response_inputs;
+  a->surprise_sum = c->surprise_sum;
+  a->gradient = c->gradient;
+  a->reduced = c->reduced;
+  a->group = c->group;
+  a->out_scale = c->out_scale;
+  a->response_fn = c->response_fn;
+  *prog = &plan->prog;
+  return 0;
+}
+}  // namespace hgf
+
 extern "C" int hgf_filter(const hgf_plan_t* plan, const hgf_call_t* call, void* stream) {
   return launch(plan, call, static_cast<cudaStream_t>(stream), false);
 }
