@@ -1,6 +1,7 @@
 // C ABI of libpyhgf_cuda (include/pyhgf_cuda.h): plan creation (lowering the
 // flattened pyhgf network description into the kernels' Program), dispatch to
 // the kernel variant, and the host-buffer convenience entry points.
+#include <algorithm>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -41,8 +42,10 @@ void count_launches(int n) { g_launches += n; }
 int report_error(const char* msg) { return fail("%s", msg); }
 }  // namespace hgf
 
-// gradient_mode auto: parameters from which the reverse sweep is taken (measured crossover: DESIGN.md §3.1)
-constexpr int kReverseFromParams = 13;
+// gradient_mode auto: the reverse sweep is taken when forward mode would need this many passes (4 filter parameters + 1
+// response parameter each).  Measured: the sweep costs 3.4-3.6 plain filters whatever P is, one
+// forward-mode pass 1.4-2.5, two passes 3.6-6.6.
+constexpr int kReverseFromPasses = 2;
 
 struct hgf_plan {
   Program prog;
@@ -354,7 +357,9 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
     if (c->gradient_mode == 2 && !available)
       return fail("gradient_mode = reverse: %s", plan->variant->reverse ? "the call asks for outputs only the forward-mode kernels produce"
                                                                           : "this plan's topology has no generated reverse sweep");
-    if (available && (c->gradient_mode == 2 || c->n_params >= kReverseFromParams)) {
+    const int n_resp = lists.n_params - lists.n_filter;
+    const int forward_passes = std::max((lists.n_filter + 3) / 4, n_resp);
+    if (available && (c->gradient_mode == 2 || forward_passes >= kReverseFromPasses)) {
       lists.n_filter = lists.n_params;
       const cudaError_t rerr = plan->variant->reverse(plan->prog, lists, a, c->dtype, stream, &n_launched);
       g_launches += n_launched;

@@ -1439,7 +1439,7 @@ class Network:
         response_function : one of ``pyhgf_b200.response``'s functions (or its name): fused into the time loop.
         record : ``[(node, attribute), ...]`` leaves to record at every step -> ``result.trajectories``.
         gradient : also return d(surprise)/d(parameters) (``hgf_logp_grad``).  ``True`` lets the library pick between
-            forward-mode tangents in the filter's registers and the checkpointed reverse sweep (taken from 13 parameters
+            forward-mode tangents in the filter's registers and the checkpointed reverse sweep (taken from 5 filter parameters
             on, where the topology has a generated one); ``"forward"`` / ``"reverse"`` force one.
         group / n_groups : sum ``out_scale * surprise`` of the instances of each group (e.g. chain) on the device.
         fused_reduce : a ``pyhgf_b200.distributed.FusedReduce``: the group sums are all-reduced over the ranks

@@ -15,11 +15,10 @@ Here the adjoint of ONE time step is written out ahead of time, as straight-line
     clip`` follow the selected branch.
 
 csrc/hgf_reverse.cuh holds the kernel around it: a forward sweep that stores the carried beliefs of every step (the
-checkpoints: 2 floats per continuous node), then the backward sweep over time.  Cost is ~5 forward passes whatever the
-number of parameters; the forward-mode kernels (hgf_math.cuh, Dual<>) cost 1 + ~0.3 per parameter up to 4 and a whole
-extra pass per further 4; measured, the sweep costs ~8.5 forward passes (165-240 registers per thread), so the library
-takes it from 13 parameters on (crossover at 9 for the 4-node continuous HGF, 14 for the 3-level binary one: DESIGN.md §3.1,
-profiles/r2_grad_scaling.log).
+checkpoints: 2 floats per continuous node), then the backward sweep over time.  Measured, the sweep costs 3.4-3.6 plain
+filters whatever the number of parameters; the forward-mode kernels (hgf_math.cuh, Dual<>) cost 1.4-2.5 plain filters per
+pass of up to 4 filter parameters + 1 response parameter, so the library takes the sweep as soon as forward mode would
+need a second pass (profiles/r2_grad_scaling.log).
 
     python -m pyhgf_b200.revgen        # (re)writes csrc/generated/reverse_*.h for the BASELINE topologies
 """

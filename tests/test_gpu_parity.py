@@ -406,8 +406,9 @@ def test_reverse_sweep_matches_dual_oracle(G, R, datasets, dtype):
 
 
 def test_reverse_sweep_dispatch(G, R, datasets):
-    """gradient=True takes the reverse sweep from 13 parameters on (one launch instead of four forward-mode passes) and the
-    two kernels agree; asking for it where it cannot run is an error, not a silent fallback."""
+    """gradient=True takes the reverse sweep as soon as forward mode would need a second pass (here 13 parameters: one launch
+    instead of four), keeps forward mode for 4 filter parameters + 1 response parameter, and the two kernels agree; asking
+    for the sweep where it cannot run is an error, not a silent fallback."""
     from pyhgf_b200 import _lib
 
     u, y = datasets["u"], datasets["y"]
@@ -429,6 +430,22 @@ def test_reverse_sweep_dispatch(G, R, datasets):
     for k in keys:
         a, b = auto.gradient[k].cpu().numpy(), fwd.gradient[k].cpu().numpy()
         assert np.allclose(a, b, rtol=1e-7, atol=1e-7 * np.abs(b).max()), k
+    net32 = nets.binary3(G.Network, dtype="float32")
+    for n_keys, launches in ((5, 1), (6, 1)):  # 4 filter parameters + the temperature: ONE forward-mode pass; 5 + 1: the sweep
+        sub = dict(zip(keys[:n_keys], vals[:n_keys]))
+        before = _lib.launch_count()
+        few = net32.batch(u, sub, gradient=True, **kw)
+        assert _lib.launch_count() - before == launches
+        assert few._call.gradient_mode == 0
+        before = _lib.launch_count()
+        ref = net32.batch(u, sub, gradient="forward", **kw)
+        assert _lib.launch_count() - before == (1 if n_keys == 5 else 2)
+        for k in keys[:n_keys]:
+            a, b = few.gradient[k].cpu().numpy(), ref.gradient[k].cpu().numpy()
+            if n_keys == 5:
+                assert np.array_equal(a, b), k  # the same kernel
+            else:
+                assert np.allclose(a, b, rtol=1e-3, atol=1e-3 * np.abs(b).max()), k
     with pytest.raises(_lib.BackendError, match="reverse"):
         net.batch(u, dict(zip(keys[:3], vals[:3])), gradient="reverse", record=[(1, "mean")], **kw)
     with pytest.raises(_lib.BackendError, match="no generated reverse sweep"):

@@ -1,6 +1,7 @@
 #!/bin/bash
+# One short gpurun call: the GPU suite (optionally a -k filter as $1) and smoke.
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu.log
-timeout 600 python tools/bench_specialise.py > gpurun_out/specialise.log 2>&1
-timeout 300 python bench.py --no-cpu > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err
-timeout 300 python tools/bench_ef.py > gpurun_out/bench_ef.log 2>&1
+if [ -n "$1" ]; then timeout 1500 python -m pytest tests -m gpu -q -k "$1" > gpurun_out/pytest_gpu.log 2>&1; else timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; fi
+echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
+tail -30 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log
