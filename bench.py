@@ -279,16 +279,37 @@ def cpu_model():
     return "unknown"
 
 
+CPU_VARIANTS = {
+    "simd": "float32, instance-vectorised (AVX-512 / AVX2 vectors of instances, libmvec), OpenMP over vectors; logp+grad by the generated reverse sweep "
+            "(oracle/hgf_simd.cpp) -- what jit(vmap(grad)) on XLA-CPU does",
+    "f32": "float32 scalar per instance (Dual<float> forward-mode tangents for logp+grad), OpenMP over instances (oracle/hgf_oracle.cpp)",
+    "f64": "float64 scalar per instance (Dual<double>), OpenMP over instances",
+}
+
+
+def best_cpu_variant(config: int) -> str:
+    """The fastest CPU arm that covers the configuration: the instance-vectorised one for the 3-level binary and 4-node
+    continuous HGFs (configs 2, 3, 4); the 16-node network (volatile-state nodes) has the scalar port only."""
+    return "f32" if config == 5 else "simd"
+
+
 def oracle_eval(w: Workload, variant: str, n_threads: int):
-    """One evaluation of workload `w`'s LOCAL shard by the oracle port; returns seconds.
-    variant "f32": the reference's arithmetic width (float32; Dual<float> tangents for logp+grad);
-            "f64": Dual<double> / double (what round 1 timed)."""
+    """One evaluation of workload `w`'s LOCAL shard by a CPU restatement of the reference's algorithm; returns seconds.
+    variant: see CPU_VARIANTS ("simd" is the arm the headline ratio is taken against where it exists)."""
     from oracle import network as onet
 
-    o = w.build(onet.Network if variant == "f32" else (lambda: onet.Network(dtype="float64"))).create_belief_propagation_fn()
+    o = w.build(onet.Network if variant != "f64" else (lambda: onet.Network(dtype="float64"))).create_belief_propagation_fn()
     slots = []
     for k in w.keys:
         slots.append(o.slot(-1, "response_parameter", k[1]) if k[0] == "response_parameter" else o.slot(k[0], k[1]))
+    if variant == "simd":
+        from oracle import simd
+
+        simd.lib()  # (built where it runs: not part of the timed region)
+        t0 = time.perf_counter()
+        simd.batch(o, w.series, slots, w.params, w.response, resp_inputs=w.resp_inputs, group_size=w.group_size, gradient=w.gradient,
+                   n_threads=n_threads)
+        return time.perf_counter() - t0
     series = w.series.astype(np.float64)
     params = w.params.astype(np.float64)
     ri = None if w.resp_inputs is None else w.resp_inputs.astype(np.float64)
@@ -304,7 +325,7 @@ def oracle_eval(w: Workload, variant: str, n_threads: int):
 def cpu_sample(config: int, budget_s: float, variant: str = "f32"):
     """A bounded sample of the configuration on the host cores: scale the batch so that one evaluation takes ~budget_s."""
     cores = host_cores()
-    probe = Workload(config, 0, 1, scale=1.0 / 128)
+    probe = Workload(config, 0, 1, scale=1.0 / (16 if variant == "simd" else 128))  # (large enough to amortise the thread start-up)
     dt = oracle_eval(probe, variant, cores)  # also warms the library
     dt = oracle_eval(probe, variant, cores)
     per_unit = dt / max(probe.units_per_eval, 1)
@@ -315,27 +336,39 @@ def cpu_sample(config: int, budget_s: float, variant: str = "f32"):
 
 
 def cpu_baseline_leg(config: int, budget_s: float = 12.0):
-    w, cores = cpu_sample(config, budget_s)
-    dt = oracle_eval(w, "f32", cores)
-    return {"value": w.units_per_eval / dt, "unit": "node-updates/s", "cores": cores, "kind": "port", "variant": "float32 scalar per instance, OpenMP over instances",
-            "sample": f"{w.workload} -- one evaluation, {dt:.2f} s", "cpu": cpu_model()}
+    variant = best_cpu_variant(config)
+    w, cores = cpu_sample(config, budget_s if variant != "simd" else 3.0, variant)
+    oracle_eval(w, variant, cores)
+    dt = min(oracle_eval(w, variant, cores) for _ in range(2 if variant == "simd" else 1))
+    out = {"value": w.units_per_eval / dt, "unit": "node-updates/s", "cores": cores, "kind": "port", "variant": CPU_VARIANTS[variant],
+           "sample": f"{w.workload} -- one evaluation, {dt:.2f} s", "cpu": cpu_model()}
+    if variant == "simd":
+        ws, _ = cpu_sample(config, 4.0, "f32")
+        out["scalar_value"] = ws.units_per_eval / oracle_eval(ws, "f32", cores)
+        out["scalar_variant"] = CPU_VARIANTS["f32"]
+    return out
 
 
 def run_reference(args):
     """--impl reference: the reference's algorithm on the host cores.  pyhgf's own implementation is Python/JAX (+ Rust);
-    neither jax/jaxlib nor cargo exist in this image, so the timed arm is the oracle port (oracle/hgf_oracle.cpp, OpenMP over
-    instances, all host threads): float32 like the reference (the line's `value`), and the float64 figure beside it."""
+    neither jax/jaxlib nor cargo exist in this image, so the timed arm is a C++ restatement of its algorithm under oracle/, on
+    all host threads: the instance-vectorised float32 arm (oracle/hgf_simd.cpp -- float32 SIMD across the batch and reverse-mode
+    gradients, as XLA-CPU would run jit(vmap(grad))) where it covers the configuration, else the scalar port; the scalar
+    float32 / float64 figures are reported beside it."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    variant = best_cpu_variant(args.config)
     budget = min(8.0, 90.0 / max(1, args.steps + args.warmup))  # whole run within a few minutes
-    w, cores = cpu_sample(args.config, budget)
+    w, cores = cpu_sample(args.config, budget, variant)
     for _ in range(args.warmup):
-        oracle_eval(w, "f32", cores)
-    times = [oracle_eval(w, "f32", cores) for _ in range(args.steps)]
+        oracle_eval(w, variant, cores)
+    times = [oracle_eval(w, variant, cores) for _ in range(args.steps)]
     total = float(sum(times))
     value = w.units_per_eval * args.steps / total
-    t64 = oracle_eval(w, "f64", cores)
+    ws, _ = cpu_sample(args.config, 4.0, "f32")
+    t32 = oracle_eval(ws, "f32", cores)
+    t64 = oracle_eval(ws, "f64", cores)
     full = Workload(args.config, 0, 1)
     same = w.units_per_eval == full.units_per_eval
     sample = f"{w.workload} -- one evaluation per step" + ("" if same else " (bounded sample of the configuration)")
@@ -344,9 +377,10 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
         "scaling": w.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": w.workload, "sample": sample, "same_config": bool(same)},
-        "cpu_baseline": {"value": value, "unit": "node-updates/s", "cores": cores, "kind": "port", "variant": "float32 scalar per instance, OpenMP over instances",
-                         "sample": sample, "cpu": cpu_model(), "value_float64": w.units_per_eval / t64,
-                         "note": "neither figure is the reference (JAX / Rust are not installable here): both time the C++ restatement of its algorithm"},
+        "cpu_baseline": {"value": value, "unit": "node-updates/s", "cores": cores, "kind": "port", "variant": CPU_VARIANTS[variant],
+                         "sample": sample, "cpu": cpu_model(), "value_scalar_float32": ws.units_per_eval / t32,
+                         "value_scalar_float64": ws.units_per_eval / t64,
+                         "note": "none of these is the reference itself (JAX / Rust are not installable here): all time C++ restatements of its algorithm"},
         "e2e": {"value": value, "unit": "node-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

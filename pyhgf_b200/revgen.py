@@ -26,6 +26,7 @@ need a second pass (profiles/r2_grad_scaling.log).
 from __future__ import annotations
 
 import os
+import re
 
 from . import _lib
 from .topology import get_update_sequence
@@ -521,7 +522,7 @@ def generate(name, network_like, vol_updates="unbounded", mean_field=False, inpu
     all_written = set().union(*[set(op.writes) for op in ops if op is not None])
     carried = sorted(live_in & all_written)
     out = [f"// GENERATED by pyhgf_b200/revgen.py -- reverse sweep of topology \"{name}\" ({len(edges)} nodes); do not edit.\n",
-           "#pragma once\n#include \"hgf_math.cuh\"\n#include \"hgf_program.h\"\n\nnamespace hgf {\n\n",
+           "#pragma once\n#include \"hgf_math.cuh\"\n#include \"hgf_program.h\"\n\n#ifndef HGF_LIT\n#define HGF_LIT(c) F(c)\n#endif\n\nnamespace hgf {\n\n",
            f"template <class F> struct Rev_{name} {{\n",
            f"  static constexpr int kSlots = {L.n_slots}, kNodes = {len(edges)}, kCarried = {len(carried)}, kInputs = {len(inputs)};\n",
            f"  static constexpr int kSlotResp = {L.slot_resp};\n"]
@@ -582,7 +583,9 @@ def generate(name, network_like, vol_updates="unbounded", mean_field=False, inpu
     for fn, (op, r) in resp_ops.items():
         out.append(f"    case {fn}: {{\n" + "\n".join(_emit_forward(op, "      ")) + "\n" + "\n".join(_emit_reverse(op, {r.name: "seed"}, "      ")) + "\n      break;\n    }\n")
     out.append("    default: break;\n    }\n  }\n};\n\n}  // namespace hgf\n")
-    return "".join(out)
+    # numeric literals go through HGF_LIT, so that the same straight-line code also compiles with F a SIMD vector type
+    # (oracle/hgf_simd.cpp, the instance-vectorised CPU arm of bench.py), where a functional cast from a scalar does not exist
+    return re.sub(r"\bF\((-?[0-9][0-9.e+\-]*)\)", r"HGF_LIT(\1)", "".join(out))
 
 
 def main():
