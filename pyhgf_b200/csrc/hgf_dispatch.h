@@ -12,7 +12,8 @@ using RunFn = cudaError_t (*)(const Program&, const CallLists&, const ScanArgs&,
                               int* n_launched);
 
 // The generated reverse sweep of a topology (hgf_reverse.cuh), when there is one: logp + gradient of a plain call
-// (per-instance sums, optional group reduction; no trajectories / pointwise output / fused cross-GPU reduction).
+// (per-instance sums, optional group reduction; no trajectories / pointwise output / fused cross-GPU reduction; every
+// response function).
 using ReverseFn = cudaError_t (*)(const Program&, const CallLists&, const ScanArgs&, int dtype, cudaStream_t, int* n_launched);
 
 struct KernelVariant {

@@ -63,6 +63,7 @@ HGF_D F reverse_instance(const Program& prog, const CallLists& lists, const Scan
 
   // ---- 1. forward, checkpointing the carried beliefs
   F total = F(0);
+  bool node1_mean_nan = false;  // total_gaussian_surprise's any-NaN rule (response.py:86-89), as in hgf_scan.cuh
   for (int t = 0; t < T; ++t) {
 #pragma unroll
     for (int c = 0; c < Rev::kCarried; ++c) state[t * plane + c * N + n] = s[Rev::carried_slot(c)];
@@ -72,6 +73,7 @@ HGF_D F reverse_instance(const Program& prog, const CallLists& lists, const Scan
     observe(t);
     Rev::update(s, dt, log_dt, cap);
     total = total + Rev::response(fn, s, resp ? HGF_LDG(resp + t) : F(0));
+    if (fn == RESP_TOTAL_GAUSSIAN && Rev::kNodes > 1 && b_isnan(s[1 * NF + F_MEAN])) node1_mean_nan = true;
   }
 
   // ---- 2. backward
@@ -98,6 +100,7 @@ HGF_D F reverse_instance(const Program& prog, const CallLists& lists, const Scan
   }
 
   const F scale = static_cast<F>(args.out_scale);
+  if (node1_mean_nan) total = b_inf<F>();  // the selected branch of the reference's jnp.where is a constant: zero gradient
   if (active) {
     if (args.surprise_sum) static_cast<F*>(args.surprise_sum)[n] = scale * total;
     if (args.gradient) {
@@ -108,7 +111,7 @@ HGF_D F reverse_instance(const Program& prog, const CallLists& lists, const Scan
 #pragma unroll
         for (int k = 0; k < Rev::kSlots; ++k)
           if (k == slot) g = sb[k];
-        grad[static_cast<long long>(lists.param_row[q]) * N + n] = scale * g;
+        grad[static_cast<long long>(lists.param_row[q]) * N + n] = node1_mean_nan ? F(0) : scale * g;
       }
     }
   }
@@ -119,7 +122,7 @@ HGF_D F reverse_instance(const Program& prog, const CallLists& lists, const Scan
 // float32: bounded to 7 resident blocks per SM (128 registers; ptxas spills 30-400 bytes of the undo log) so that 65 536
 // instances are one wave, like the forward-mode kernels (hgf_scan.cuh::scan_min_blocks): 3.8 -> 3.3 ms on config 4's batch
 template <class F, class Rev, bool UNIT_DT>
-__global__ void __launch_bounds__(SCAN_THREADS, sizeof(F) == 4 ? 7 : 1)
+__global__ void __launch_bounds__(SCAN_THREADS, (sizeof(F) == 4 && Rev::kNodes <= 4) ? 7 : 1)
 reverse_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLists lists, const __grid_constant__ ScanArgs args, F* state) {
   long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool active = n < args.n_instances;

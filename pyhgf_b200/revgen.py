@@ -338,56 +338,154 @@ def posterior_continuous(op, L, node, dt, log_dt, cap, exact_sigmoid):  # contin
     op.put(node, "mean", op.field(node, "expected_mean") + fv + fvol)
 
 
-def posterior_continuous_unbounded(op, L, node, dt, log_dt, cap, exact_sigmoid):
-    """continuous_node_posterior_update_unbounded.py:13-220 (hgf_ops.cuh::unbounded_mixture<true>)."""
-    t, e = op.tr, L.edges[node]
-    child = _volc(e)[0]
-    prev_var = t.max_c(op.field(child, "temp.current_variance"), 1e-128)
-    delta = op.field(child, "mean") - op.field(child, "expected_mean")
-    be = 1.0 / op.field(child, "precision") + delta * delta
-    mu_hat, pi_hat = op.field(node, "expected_mean"), op.field(node, "expected_precision")
-    kappa, omega = op.get(L.cvolc(node, 0)), op.field(child, "tonic_volatility")
+def _unbounded_mixture(t, explicit, prev_variance, c_precision, c_mean, c_expected_mean, c_expected_precision, mu_hat, pi_hat, kappa, omega,
+                       log_dt):
+    """hgf_ops.cuh::unbounded_mixture<EXPLICIT>: the two-expansion Lambert-W mixture
+    (continuous_node_posterior_update_unbounded.py:51-220; volatile_node_posterior_update_unbounded.py:12-178 with kappa = 1 and
+    no omega: explicit = False).  Returns (posterior precision, posterior mean)."""
+    prev_var = t.max_c(prev_variance, 1e-128)
+    delta = c_mean - c_expected_mean
+    be = 1.0 / c_precision + delta * delta
     log_prev_var = t.log(prev_var)
-    gamma = log_dt + kappa * mu_hat + omega
+    gamma = (log_dt + kappa * mu_hat + omega) if explicit else (log_dt + mu_hat)
     w1 = t.sigmoid(gamma - log_prev_var)
-    da1 = op.field(child, "expected_precision") * be - 1.0
-    pi1 = pi_hat + 0.5 * (kappa * kappa) * w1 * (1.0 - w1)
-    mu1 = mu_hat + (kappa * w1 / (2.0 * pi1)) * da1
-    pi_y = pi_hat / (kappa * kappa)
+    da1 = c_expected_precision * be - 1.0
+    if explicit:
+        pi1 = pi_hat + 0.5 * (kappa * kappa) * w1 * (1.0 - w1)
+        mu1 = mu_hat + (kappa * w1 / (2.0 * pi1)) * da1
+        pi_y = pi_hat / (kappa * kappa)
+    else:
+        pi1 = pi_hat + 0.5 * w1 * (1.0 - w1)
+        mu1 = mu_hat + (w1 / (2.0 * pi1)) * da1
+        pi_y = pi_hat
     log_w_arg = t.log(be) - t.log(2.0 * pi_y) + 0.5 / pi_y - gamma
     w_arg = t.exp(t.min_c(log_w_arg, "LOGMAX"))
     y_star = gamma + t.lambert_w0(w_arg) - 0.5 / pi_y
-    x_star = (y_star - log_dt - omega) / kappa
-    log_s2 = log_dt + kappa * x_star + omega
+    if explicit:
+        x_star = (y_star - log_dt - omega) / kappa
+        log_s2 = log_dt + kappa * x_star + omega
+    else:
+        x_star = y_star - log_dt
+        log_s2 = log_dt + x_star
     log_den = t.logaddexp(log_prev_var, log_s2)
     w2 = t.sigmoid(log_s2 - log_prev_var)
     da2 = be * t.exp(-log_den) - 1.0
-    k2 = kappa * kappa
-    pi2_full = pi_hat + 0.5 * k2 * w2 * (w2 + (2.0 * w2 - 1.0) * da2)
-    pi2_alt = pi_hat + 0.5 * k2 * w2 * (1.0 - w2)
+    if explicit:
+        k2 = kappa * kappa
+        pi2_full = pi_hat + 0.5 * k2 * w2 * (w2 + (2.0 * w2 - 1.0) * da2)
+        pi2_alt = pi_hat + 0.5 * k2 * w2 * (1.0 - w2)
+    else:
+        pi2_full = pi_hat + 0.5 * w2 * (w2 + (2.0 * w2 - 1.0) * da2)
+        pi2_alt = pi_hat + 0.5 * w2 * (1.0 - w2)
     pi2_safe = t.select(f"{pi2_full.name} <= F(0)", pi2_alt, pi2_full)
-    mu2_safe = x_star + (0.5 * kappa * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe
+    if explicit:
+        mu2_safe = x_star + (0.5 * kappa * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe
+    else:
+        mu2_safe = x_star + (0.5 * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe
     ok = f"{t.isfinite(pi2_safe)} && {t.isfinite(mu2_safe)}"
     pi2 = t.select(ok, pi2_safe, pi1)
     mu2 = t.select(ok, mu2_safe, mu1)
-    l1 = t.logaddexp(log_prev_var, log_dt + kappa * mu1 + omega)
+    arg1 = (log_dt + kappa * mu1 + omega) if explicit else (log_dt + mu1)
+    arg2 = (log_dt + kappa * mu2 + omega) if explicit else (log_dt + mu2)
+    l1 = t.logaddexp(log_prev_var, arg1)
     e1 = mu1 - mu_hat
     i1 = -0.5 * l1 - 0.5 * be * t.exp(-l1) - 0.5 * pi_hat * (e1 * e1)
-    l2 = t.logaddexp(log_prev_var, log_dt + kappa * mu2 + omega)
+    l2 = t.logaddexp(log_prev_var, arg2)
     e2 = mu2 - mu_hat
     i2 = -0.5 * l2 - 0.5 * be * t.exp(-l2) - 0.5 * pi_hat * (e2 * e2)
     b = t.sigmoid(i2 - i1)
     post_mean = (1.0 - b) * mu1 + b * mu2
     dm = mu1 - mu2
     post_precision = 1.0 / ((1.0 - b) / pi1 + b / pi2 + b * (1.0 - b) * (dm * dm))
-    op.put(node, "precision", t.min_c(post_precision, cap))
-    op.put(node, "mean", post_mean)
+    return post_precision, post_mean
+
+
+def posterior_continuous_unbounded(op, L, node, dt, log_dt, cap, exact_sigmoid):
+    """continuous_node_posterior_update_unbounded.py:13-48 (reads only the first volatility child, never its `observed` flag)."""
+    t, e = op.tr, L.edges[node]
+    child = _volc(e)[0]
+    pi, mu = _unbounded_mixture(
+        t, True, op.field(child, "temp.current_variance"), op.field(child, "precision"), op.field(child, "mean"),
+        op.field(child, "expected_mean"), op.field(child, "expected_precision"), op.field(node, "expected_mean"),
+        op.field(node, "expected_precision"), op.get(L.cvolc(node, 0)), op.field(child, "tonic_volatility"), log_dt)
+    op.put(node, "precision", t.min_c(pi, cap))
+    op.put(node, "mean", mu)
+
+
+# volatile-state nodes (hgf_ops.cuh: predict_volatile, pe_volatile, posterior_volatile)
+def predict_volatile(op, L, node, dt, log_dt, cap, exact_sigmoid):  # prediction/volatile.py:230-309
+    t, e = op.tr, L.edges[node]
+    variance = 1.0 / op.field(node, "precision")
+    op.put(node, "temp.current_variance", variance)
+    omega_vol = _nan_unless_positive(t, dt * t.exp(op.field(node, "tonic_volatility_vol")))
+    pi_hat_vol = 1.0 / (1.0 / op.field(node, "precision_vol") + omega_vol)
+    mu_hat_vol = op.field(node, "mean_vol")
+    op.put(node, "expected_mean_vol", mu_hat_vol)
+    op.put(node, "expected_precision_vol", pi_hat_vol)
+    op.put(node, "temp.effective_precision_vol", omega_vol * pi_hat_vol)
+    log_vol = mu_hat_vol + 1.0 / (2.0 * pi_hat_vol)
+    omega = _nan_unless_positive(t, dt * t.exp(log_vol))
+    pi_cond = 1.0 / (variance + omega)
+    if not _vp(e):
+        pi_marg = pi_cond
+    else:
+        var = t.lift(0.0)
+        for k, p in enumerate(_vp(e)):
+            c = dt * op.get(L.cvp(node, k))
+            var = var + (c * c) / op.field(p, "expected_precision")
+        pi_marg = 1.0 / (variance + omega + var)
+    lam = op.field(node, "autoconnection_strength")
+    drift = t.lift(0.0)  # (a volatile node has no tonic drift, volatile.py:51-108)
+    for k, p in enumerate(_vp(e)):
+        _linear_only(L.edges, p, node)
+        drift = drift + op.get(L.cvp(node, k)) * op.field(p, "expected_mean")
+    op.put(node, "expected_mean", lam * op.field(node, "mean") + dt * drift)
+    if not _vc(e) and not _volc(e) and not _volp(e):
+        op.put(node, "expected_precision", op.field(node, "precision"))
+        op.put(node, "temp.conditional_expected_precision", op.field(node, "precision"))
+        op.put(node, "temp.effective_precision", t.lift(0.0))
+    else:
+        op.put(node, "expected_precision", pi_marg)
+        op.put(node, "temp.conditional_expected_precision", pi_cond)
+        op.put(node, "temp.effective_precision", omega * pi_marg)
+
+
+def pe_volatile(op, L, node, dt, log_dt, cap, exact_sigmoid):  # prediction_error/volatile.py:13-154 + the implicit level's posterior
+    t = op.tr
+    mean, mu_hat = op.field(node, "mean"), op.field(node, "expected_mean")
+    delta = mean - mu_hat
+    pi_hat = op.field(node, "expected_precision")
+    precision = op.field(node, "precision")
+    vope = pi_hat / precision + pi_hat * (delta * delta) - 1.0
+    op.put(node, "temp.value_prediction_error", delta)
+    op.put(node, "temp.volatility_prediction_error", vope)
+    pi, mu = _unbounded_mixture(t, False, op.field(node, "temp.current_variance"), precision, mean, mu_hat, pi_hat,
+                                op.field(node, "expected_mean_vol"), op.field(node, "expected_precision_vol"), None, None, log_dt)
+    op.put(node, "precision_vol", t.min_c(pi, cap))
+    op.put(node, "mean_vol", mu)
+
+
+def posterior_volatile(op, L, node, dt, log_dt, cap, exact_sigmoid):  # posterior/volatile/posterior_update_value_level.py:11-245
+    t, e = op.tr, L.edges[node]
+    pi_hat = op.field(node, "expected_precision")
+    pi = pi_hat
+    for k, c in enumerate(_vc(e)):
+        _linear_only(L.edges, node, c)
+        psi = op.get(L.cvc(node, k))
+        pi = pi + (psi * psi) * _child_precision_weight(op, L, c)
+    pi = t.min_c(t.maximum(pi, pi_hat), cap)
+    op.put(node, "precision", pi)
+    gain = t.lift(0.0)
+    for k, c in enumerate(_vc(e)):
+        gain = gain + ((op.get(L.cvc(node, k)) * _child_gain_precision(op, L, c)) / pi) * op.field(c, "temp.value_prediction_error")
+    op.put(node, "mean", op.field(node, "expected_mean") + gain)
 
 
 OPS = {
     _lib.OPS["PRED_BINARY"]: predict_binary, _lib.OPS["PRED_CONT"]: predict_continuous,
     _lib.OPS["PE_BINARY"]: pe_binary, _lib.OPS["PE_CONT"]: pe_continuous,
     _lib.OPS["POST_CONT"]: posterior_continuous, _lib.OPS["POST_CONT_UNBOUNDED"]: posterior_continuous_unbounded,
+    _lib.OPS["PRED_VOLATILE"]: predict_volatile, _lib.OPS["PE_VOLATILE"]: pe_volatile, _lib.OPS["POST_VOLATILE"]: posterior_volatile,
 }
 
 
@@ -410,6 +508,15 @@ def response(op, L, fn, y, inputs):
     t = op.tr
     if fn == 1:  # first_level_gaussian_surprise: node 0's observation against node 1's prediction
         return _nan_to_inf(t, _gaussian_surprise(t, op.field(0, "mean", diff=False), op.field(1, "expected_mean"), op.field(1, "expected_precision")))
+    if fn == 2:  # total_gaussian_surprise, response.py:51-89: every continuous node (its any-NaN rule is the kernel's)
+        if not any(e.node_type == 2 for e in L.edges):
+            raise Unsupported("no continuous node")
+        total = t.lift(0.0)
+        for n, e in enumerate(L.edges):
+            if e.node_type == 2:
+                total = total + _gaussian_surprise(t, op.field(n, "mean", diff=n not in inputs), op.field(n, "expected_mean"),
+                                                   op.field(n, "expected_precision"))
+        return total
     if fn == 3:  # first_level_binary_surprise
         total = t.lift(0.0)
         for n in inputs:
@@ -426,7 +533,7 @@ def response(op, L, fn, y, inputs):
     raise Unsupported(f"response function {fn}")
 
 
-RESPONSES = (1, 3, 4, 5)
+RESPONSES = (1, 2, 3, 4, 5)
 
 
 # ----------------------------------------------------------------------------------------------------------------------
@@ -487,8 +594,8 @@ def generate(name, network_like, vol_updates="unbounded", mean_field=False, inpu
     edges = network_like.edges
     if vol_updates != "unbounded" or mean_field:
         raise Unsupported("the generated reverse sweep covers the default scheme (unbounded, relaxed)")
-    if any(e.node_type not in (1, 2) for e in edges):
-        raise Unsupported("the generated reverse sweep covers binary and continuous state nodes")
+    if any(e.node_type not in (1, 2, 6) for e in edges):
+        raise Unsupported("the generated reverse sweep covers binary, continuous and volatile state nodes")
     L = Layout(edges)
     pred, upd = get_update_sequence(network_like, vol_updates, mean_field)
     if inputs is None:
@@ -593,7 +700,7 @@ def main():
 
     os.makedirs(GEN, exist_ok=True)
     names = []
-    for name in ("binary2", "binary3", "continuous2", "continuous3"):
+    for name in ("binary2", "binary3", "continuous2", "continuous3", "ghgf8", "ghgf16"):
         spec = codegen.TOPOLOGIES[name]
         text = generate(name, spec[0](), spec[1], spec[2])
         codegen._write_if_changed(os.path.join(GEN, f"reverse_{name}.h"), text)

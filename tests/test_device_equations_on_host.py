@@ -102,3 +102,42 @@ def test_generated_reverse_sweep_is_the_oracles_gradient(box, datasets):
         assert np.array_equal(logp, want_s), build.__name__
         for i, k in enumerate(keys):
             assert np.allclose(grad[i], want_g[i], rtol=1e-9, atol=1e-10 * np.abs(want_g[i]).max()), (build.__name__, k)
+
+
+def test_generated_reverse_sweep_of_the_16_node_network(box):
+    """BASELINE config 5's network (continuous + volatile-state nodes, two components): the generated reverse sweep compiled
+    for the host, float64, against the Dual<double> oracle -- all 12 volatilities and six other attributes (an initial belief, a
+    volatility-level precision, an autoconnection, a value and a volatility coupling, a drift), under both Gaussian response
+    functions (total_gaussian_surprise sums every continuous node)."""
+    import ctypes as C
+
+    from pyhgf_b200.network import Network
+
+    hostsim, _ = box
+    lib = hostsim.build(["@"])
+    fp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rng = np.random.default_rng(5)
+    n, T = 24, 150
+    x = np.ascontiguousarray(nets.ar1_series(T, 4, seed=3), dtype=np.float64)
+    net = nets.ghgf16(Network, dtype="float64")
+    net.create_belief_propagation_fn()
+    plan = net._get_plan(4)
+    attrs = np.ascontiguousarray(net._flatten(plan), dtype=np.float64)
+    o = nets.ghgf16(onet.Network, dtype="float64").create_belief_propagation_fn()
+    draw = {"tonic_volatility": lambda: rng.uniform(-5, -3, n), "tonic_volatility_vol": lambda: rng.uniform(-5, -3, n),
+            "mean": lambda: rng.uniform(-0.3, 0.3, n), "precision_vol": lambda: np.exp(rng.uniform(-0.3, 0.3, n)),
+            "autoconnection_strength": lambda: rng.uniform(0.9, 1.0, n), "tonic_drift": lambda: rng.uniform(-0.01, 0.01, n)}
+    all_keys = ([(i, "tonic_volatility") for i in range(4, 12)] + [(i, "tonic_volatility_vol") for i in range(12, 16)] +
+                [(12, "mean"), (14, "precision_vol"), (13, "autoconnection_strength"), (5, "value_coupling_parents", 0),
+                 (9, "volatility_coupling_children", 0), (6, "tonic_drift")])
+    for fn, rname in ((2, "total_gaussian_surprise"), (1, "first_level_gaussian_surprise")):
+        for lo in range(0, len(all_keys), 6):  # (the oracle carries at most 8 tangents)
+            keys = all_keys[lo:lo + 6]
+            p = np.ascontiguousarray(np.stack([draw.get(k[1], lambda: rng.uniform(0.8, 1.2, n))() for k in keys]))
+            slots = np.array([net._resolve_slot(plan, k) for k in keys], dtype=np.int32)
+            logp, grad = np.zeros(n), np.zeros((len(keys), n))
+            lib.sim_ghgf16_reverse_f64(n, T, fp(x), fp(attrs), len(keys), fp(slots), fp(p), fn, fp(logp), fp(grad))
+            want_s, want_g = o.batch_grad(x, [o.slot(*k) for k in keys], p, rname)
+            assert np.array_equal(logp, want_s), rname
+            for i, k in enumerate(keys):
+                assert np.allclose(grad[i], want_g[i], rtol=1e-9, atol=1e-10 * max(np.abs(want_g[i]).max(), 1e-300)), (rname, k)

@@ -453,6 +453,69 @@ def test_reverse_sweep_dispatch(G, R, datasets):
                                         response_function=R.first_level_gaussian_surprise, gradient="reverse")
 
 
+def test_reverse_sweep_16_node_network(G, R):
+    """BASELINE config 5's network (volatile-state nodes included): d logp / d (all 12 volatilities + 4 more attributes) by
+    the generated reverse sweep in ONE launch (gradient=True picks it: forward mode would need 4 passes through the
+    interpreter), against the Dual<double> oracle in float64 and against the float64 launch in float32."""
+    from pyhgf_b200 import _lib
+
+    n, T = 96, 200
+    x = nets.ar1_series(T, 4, seed=3)
+    keys = ([(i, "tonic_volatility") for i in range(4, 12)] + [(i, "tonic_volatility_vol") for i in range(12, 16)] +
+            [(12, "mean"), (13, "autoconnection_strength"), (5, "value_coupling_parents", 0), (9, "volatility_coupling_children", 0)])
+    vals = ([_grid(n, -5, -3, 1 + i) for i in range(12)] + [_grid(n, -0.3, 0.3, 20), _grid(n, 0.9, 1.0, 21), _grid(n, 0.8, 1.2, 22), _grid(n, 0.8, 1.2, 23)])
+    for rfn, rname in ((R.total_gaussian_surprise, "total_gaussian_surprise"), (R.first_level_gaussian_surprise, "first_level_gaussian_surprise")):
+        net = nets.ghgf16(G.Network, dtype="float64")
+        before = _lib.launch_count()
+        res = net.batch(x, dict(zip(keys, vals)), response_function=rfn, gradient=True)
+        assert res.kernel_name == "static:ghgf16"
+        assert _lib.launch_count() - before == 1
+        o = nets.ghgf16(onet.Network, dtype="float64").create_belief_propagation_fn()
+        p = np.stack(vals)
+        for lo in range(0, len(keys), 8):  # (the oracle carries at most 8 tangents)
+            sl = slice(lo, lo + 8)
+            want_s, want_g = _oracle_grad_subset(o, x, keys, p, sl, rname)
+            assert np.allclose(res.surprise.cpu().numpy(), want_s, rtol=1e-9)
+            for i, k in enumerate(keys[sl]):
+                got = res.gradient[k].cpu().numpy()
+                assert np.allclose(got, want_g[i], rtol=1e-7, atol=1e-7 * max(np.abs(want_g[i]).max(), 1e-300)), (rname, k)
+        r32 = nets.ghgf16(G.Network, dtype="float32").batch(x, dict(zip(keys, vals)), response_function=rfn, gradient="reverse")
+        s64 = res.surprise.cpu().numpy()
+        assert np.median(np.abs(r32.surprise.double().cpu().numpy() - s64) / np.abs(s64)) < 1e-5
+        for k in keys:
+            g64 = res.gradient[k].cpu().numpy()
+            err = np.abs(r32.gradient[k].double().cpu().numpy() - g64) / np.maximum(np.abs(g64), 1e-3 * max(np.abs(g64).max(), 1e-300))
+            assert np.median(err) < 1e-3, (rname, k, float(np.median(err)))
+
+
+def _oracle_grad_subset(o, x, keys, p, sl, rname):
+    """Dual oracle gradient wrt the parameters keys[sl] with EVERY parameter of `keys` set per instance: the oracle carries at
+    most 8 tangents, so the parameters outside the subset are written into the network's attributes, one instance at a time."""
+    n = p.shape[1]
+    all_slots = [o.slot(*k) for k in keys]
+    sub = list(range(*sl.indices(len(keys))))
+    rest = [i for i in range(len(keys)) if i not in sub]
+    want_s, want_g = np.zeros(n), np.zeros((len(sub), n))
+    for j in range(n):
+        saved = {}
+        for i in rest:
+            node, key = keys[i][0], keys[i][1]
+            a = o.attributes[node]
+            if len(keys[i]) == 3:
+                saved[i] = np.array(a[key], dtype=np.float64).copy()
+                arr = np.array(a[key], dtype=np.float64)
+                arr[keys[i][2]] = p[i, j]
+                a[key] = arr
+            else:
+                saved[i] = a[key]
+                a[key] = float(p[i, j])
+        s_, g_ = o.batch_grad(x, [all_slots[i] for i in sub], p[sub][:, j:j + 1], rname)
+        want_s[j], want_g[:, j] = s_[0], g_[:, 0]
+        for i in rest:
+            o.attributes[keys[i][0]][keys[i][1]] = saved[i]
+    return want_s, want_g
+
+
 def test_gradient_continuous_and_coupling(G, R, datasets):
     x = datasets["x"][:300]
     n = 64

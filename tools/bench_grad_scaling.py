@@ -1,6 +1,6 @@
 """logp + gradient cost against the number of differentiated parameters P: forward-mode tangents in the filter's registers
 (ceil(P / 4) passes) versus the generated checkpointed reverse sweep (csrc/hgf_reverse.cuh), on the BASELINE topologies.
-65 536 instances; binary3: 320 trials (config 4's shape), continuous3: 614 observations (config 2's).
+65 536 instances; binary3: 320 trials (config 4's shape), continuous3: 614 observations (config 2's); ghgf16 (config 5's network): 32 768 x 300.
 
     python tools/bench_grad_scaling.py > profiles/r2_grad_scaling.log
 """
@@ -52,7 +52,15 @@ cases["continuous3"] = dict(
             ((2, "volatility_coupling_children", 0), col(0.8, 1.2)), ((1, "volatility_coupling_parents", 0), col(0.8, 1.2)),
             ((3, "volatility_coupling_children", 0), col(0.8, 1.2)), ((2, "volatility_coupling_parents", 0), col(0.8, 1.2))])
 
-print(f"# {torch.cuda.get_device_name(0)}; N = {N} instances; ms per logp+grad launch (median of 7 after 4 warm-up launches, inputs resident)")
+# BASELINE config 5's 16-node network (volatile-state nodes): 32 768 instances x 300 steps; forward mode runs through the opcode
+# interpreter (no register-resident gradient kernels are built for it), the reverse sweep is generated (Rev_ghgf16)
+N16 = 32768
+cases["ghgf16"] = dict(
+    net=lambda: bench.net_ghgf16(Network), series=bench.ar1_series(300, 4, seed=1), resp=response.total_gaussian_surprise, resp_inputs=None, n=N16,
+    params=[((i, "tonic_volatility"), col(-5, -3)[:N16]) for i in range(4, 12)] + [((i, "tonic_volatility_vol"), col(-5, -3)[:N16]) for i in range(12, 16)] +
+           [((12, "mean"), col(-0.3, 0.3)[:N16]), ((13, "mean"), col(-0.3, 0.3)[:N16]), ((14, "mean_vol"), col(-0.3, 0.3)[:N16]), ((15, "mean_vol"), col(-0.3, 0.3)[:N16])])
+
+print(f"# {torch.cuda.get_device_name(0)}; N = {N} instances (ghgf16: {N16}); ms per logp+grad launch (median of 7 after 4 warm-up launches, inputs resident)")
 for name, c in cases.items():
     net = c["net"]()
     kw = dict(response_function=c["resp"])
@@ -60,7 +68,7 @@ for name, c in cases.items():
         kw["response_function_inputs"] = c["resp_inputs"]
     fwd0 = time_launch(net.batch(c["series"], dict(c["params"][:1]), **kw))
     print(f"{name}: forward filter alone (logp, no gradient) {fwd0:.3f} ms")
-    for P in (1, 2, 3, 4, 6, 8, 9, 12, 16):
+    for P in ((4, 8, 16) if name == "ghgf16" else (1, 2, 3, 4, 6, 8, 9, 12, 16)):
         p = dict(c["params"][:P])
         row = {"topology": name, "P": P, "forward_only_ms": fwd0}
         for mode in ("forward", "reverse"):
