@@ -114,7 +114,7 @@ def test_generated_reverse_sweep_of_the_16_node_network(box):
     from pyhgf_b200.network import Network
 
     hostsim, _ = box
-    lib = hostsim.build(["@"])
+    lib = hostsim.build(["@", "-DHOSTSIM_GHGF16"])
     fp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
     rng = np.random.default_rng(5)
     n, T = 24, 150

@@ -11,7 +11,9 @@
 #include "hgf_reverse.cuh"
 #include <generated/reverse_binary3.h>
 #include <generated/reverse_continuous3.h>
-#include <generated/reverse_ghgf16.h>
+#ifdef HOSTSIM_GHGF16
+#include <generated/reverse_ghgf16.h>  // 12 000 generated lines: only the test that needs it pays the compile (-DHOSTSIM_GHGF16)
+#endif
 #include <vector>
 
 using namespace hgf;
@@ -75,11 +77,13 @@ extern "C" void sim_continuous3_reverse_f64(int n, int T, const double* u, const
                                             double* logp, double* grad) {
   run_reverse<double, Rev_continuous3<double>>(n, T, 0, u, nullptr, attrs, n_params, slots, params, RESP_FIRST_LEVEL_GAUSSIAN, logp, grad);
 }
+#ifdef HOSTSIM_GHGF16
 // BASELINE config 5's 16-node network (continuous + volatile-state nodes), u [T][4] shared by the instances
 extern "C" void sim_ghgf16_reverse_f64(int n, int T, const double* u, const double* attrs, int n_params, const int* slots, const double* params,
                                        int response_fn, double* logp, double* grad) {
   run_reverse<double, Rev_ghgf16<double>>(n, T, 0, u, nullptr, attrs, n_params, slots, params, response_fn, logp, grad);
 }
+#endif
 extern "C" void sim_binary3(int n, int T, int group, const float* u, const float* y, const float* attrs, const int* slots,
                             const float* params, int response_fn, float* logp) {
   run<Topo_binary3, 0, 0>(n, T, group, u, y, attrs, 3, slots, params, response_fn, logp, nullptr);
