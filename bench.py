@@ -288,9 +288,8 @@ CPU_VARIANTS = {
 
 
 def best_cpu_variant(config: int) -> str:
-    """The fastest CPU arm that covers the configuration: the instance-vectorised one for the 3-level binary and 4-node
-    continuous HGFs (configs 2, 3, 4); the 16-node network (volatile-state nodes) has the scalar port only."""
-    return "f32" if config == 5 else "simd"
+    """The fastest CPU arm that covers the configuration: the instance-vectorised one covers the networks of all four."""
+    return "simd"
 
 
 def oracle_eval(w: Workload, variant: str, n_threads: int):

@@ -93,6 +93,7 @@ template <> inline vf b_lambert_w0<vf>(vf z) {
 
 #include <generated/reverse_binary3.h>
 #include <generated/reverse_continuous3.h>
+#include <generated/reverse_ghgf16.h>
 
 namespace hgf {
 
@@ -158,6 +159,7 @@ static void run_pack(const SimdCall& c, long long first, std::vector<vf>& state)
   };
   const bool want_grad = c.gradient != nullptr;
   vf total = splat(0.0f);
+  vi bad = {};  // total_gaussian_surprise's any-NaN rule (response.py:86-89): +inf, zero gradient
   for (int t = 0; t < T; ++t) {
     if (want_grad)
       for (int k = 0; k < Rev::kCarried; ++k) state[static_cast<size_t>(t) * Rev::kCarried + k] = s[Rev::carried_slot(k)];
@@ -167,7 +169,9 @@ static void run_pack(const SimdCall& c, long long first, std::vector<vf>& state)
     observe(t);
     Rev::update(s, dt, log_dt, cap);
     total = total + Rev::response(c.response_fn, s, rp[0] ? gather(rp, r_uniform, t) : splat(0.0f));
+    if (c.response_fn == RESP_TOTAL_GAUSSIAN && Rev::kNodes > 1) bad = bad | b_isnan(s[1 * NF + F_MEAN]);
   }
+  total = bad ? splat(__builtin_huge_valf()) : total;
   for (int l = 0; l < W; ++l)
     if (first + l < N) c.surprise[first + l] = total[l];
   if (!want_grad) return;
@@ -191,7 +195,7 @@ static void run_pack(const SimdCall& c, long long first, std::vector<vf>& state)
   }
   for (int q = 0; q < c.n_params; ++q)
     for (int l = 0; l < W; ++l)
-      if (first + l < N) c.gradient[static_cast<long long>(q) * N + first + l] = sb[c.param_slots[q]][l];
+      if (first + l < N) c.gradient[static_cast<long long>(q) * N + first + l] = bad[l] ? 0.0f : sb[c.param_slots[q]][l];
 }
 
 template <class Rev>
@@ -213,13 +217,18 @@ static int run(const SimdCall& c, int n_threads) {
 
 extern "C" {
 int hgf_simd_width(void) { return hgf::W; }
-int hgf_simd_n_slots(int topology) { return topology == 0 ? hgf::Rev_binary3<hgf::vf>::kSlots : topology == 1 ? hgf::Rev_continuous3<hgf::vf>::kSlots : -1; }
-// topology 0: the 3-level binary HGF, 1: the 4-node continuous HGF (the networks of BASELINE configs 2, 3, 4)
+int hgf_simd_n_slots(int topology) {
+  return topology == 0 ? hgf::Rev_binary3<hgf::vf>::kSlots : topology == 1 ? hgf::Rev_continuous3<hgf::vf>::kSlots
+       : topology == 2 ? hgf::Rev_ghgf16<hgf::vf>::kSlots : -1;
+}
+// topology 0: the 3-level binary HGF, 1: the 4-node continuous HGF, 2: the 16-node generalised HGF (the networks of the
+// BASELINE configurations)
 int hgf_simd_batch(int topology, const hgf::SimdCall* call, int n_threads) {
   if (!call || call->n_instances < 0 || call->n_steps < 0 || !call->attributes || !call->surprise) return 1;
   if (call->n_instances == 0) return 0;
   if (topology == 0) return hgf::run<hgf::Rev_binary3<hgf::vf>>(*call, n_threads);
   if (topology == 1) return hgf::run<hgf::Rev_continuous3<hgf::vf>>(*call, n_threads);
+  if (topology == 2) return hgf::run<hgf::Rev_ghgf16<hgf::vf>>(*call, n_threads);
   return 1;
 }
 }

@@ -3,8 +3,8 @@
 The reference's CPU path is ``jit(vmap(...))`` on XLA-CPU: float32, vectorised across the batch, reverse-mode gradients.
 The scalar oracle (hgf_oracle.cpp) is the parity checker; THIS is the CPU implementation bench.py times beside the GPU
 (`cpu_baseline`, `--impl reference`): 16 (AVX-512) or 8 (AVX2) instances per SIMD vector, libmvec, OpenMP, and the generated
-reverse sweep for logp + gradient.  It covers the networks of BASELINE configs 2, 3 and 4 (the 3-level binary and the 4-node
-continuous HGF, default "unbounded" scheme, unit or given time steps, every observation present).
+reverse sweep for logp + gradient.  It covers the networks of the BASELINE configurations (the 3-level binary, the 4-node
+continuous and the 16-node generalised HGF; default "unbounded" scheme, unit or given time steps, every observation present).
 
 Only tests/ and bench.py's CPU legs may import it.
 """
@@ -59,7 +59,7 @@ def build_library(force: bool = False) -> str:
     path = library_path()
     src = os.path.join(_HERE, "hgf_simd.cpp")
     gen = os.path.join(_ROOT, "pyhgf_b200", "csrc", "generated")
-    deps = [src] + [os.path.join(gen, f) for f in ("reverse_binary3.h", "reverse_continuous3.h")]
+    deps = [src] + [os.path.join(gen, f) for f in ("reverse_binary3.h", "reverse_continuous3.h", "reverse_ghgf16.h")]
     if force or not os.path.exists(path) or os.path.getmtime(path) < max(os.path.getmtime(d) for d in deps):
         cmd = ["g++", "-O3", "-std=c++17", "-fopenmp", "-shared", "-fPIC", "-Wno-attributes", "-Wno-unused-variable", "-Wno-ignored-attributes",
                *_isa()[1], "-I", os.path.join(_ROOT, "pyhgf_b200", "csrc"), "-I", "/usr/local/cuda/include", src, "-o", path, "-lmvec", "-lm"]
@@ -85,7 +85,7 @@ def width() -> int:
 
 
 def _topology(net: "onet.Network") -> int:
-    """0: the 3-level binary HGF, 1: the 4-node continuous HGF -- recognised by their edges."""
+    """0: the 3-level binary HGF, 1: the 4-node continuous HGF, 2: the 16-node generalised HGF -- recognised by their edges."""
     kinds = [e.node_type for e in net.edges]
     if net.volatility_updates != "unbounded" or net.mean_field_updates:
         raise NotImplementedError("the SIMD CPU arm covers the default scheme")
@@ -94,7 +94,10 @@ def _topology(net: "onet.Network") -> int:
         return 0
     if kinds == [2, 2, 2, 2] and e[1].value_children == (0,) and e[2].volatility_children == (1,) and e[3].volatility_children == (2,):
         return 1
-    raise NotImplementedError("the SIMD CPU arm covers the 3-level binary and the 4-node continuous HGF")
+    if kinds == [2] * 12 + [6] * 4 and all(e[4 + i].value_children == (i,) and e[8 + i].volatility_children == (4 + i,) for i in range(4)) \
+            and [e[i].value_children for i in range(12, 16)] == [(4, 5), (6, 7), (12,), (13,)]:
+        return 2
+    raise NotImplementedError("the SIMD CPU arm covers the 3-level binary, the 4-node continuous and the 16-node generalised HGF")
 
 
 def batch(net: "onet.Network", values, param_slots, params, response: str, resp_inputs=None, response_parameters=None,
@@ -132,7 +135,7 @@ def batch(net: "onet.Network", values, param_slots, params, response: str, resp_
     c.response_inputs = None if ri is None else ri.ctypes.data
     c.attributes = slots0.ctypes.data
     c.n_params, c.param_slots, c.params = len(list(param_slots)), ps.ctypes.data, params.ctypes.data
-    c.response_fn = onet.RESPONSES[response]
+    c.response_fn = 0 if response is None else onet.RESPONSES[response]  # None: the filter alone
     c.max_posterior_precision = float(net.max_posterior_precision)
     c.surprise = out.ctypes.data
     c.gradient = None if grad is None else grad.ctypes.data

@@ -86,6 +86,23 @@ def test_continuous_hgf_forward_and_gradient(datasets):
     _bulk(_rel(got, want), "continuous logp, time steps")
 
 
+def test_16_node_network_with_volatile_nodes():
+    """BASELINE config 5's network: the filter alone (what its CPU arm times), logp and the reverse-sweep gradient."""
+    x = nets.ar1_series(200, 4, seed=3)
+    o = nets.ghgf16(onet.Network).create_belief_propagation_fn()
+    keys = [(i, "tonic_volatility") for i in range(4, 10)] + [(12, "tonic_volatility_vol")]
+    rng = np.random.default_rng(1)
+    n = 70
+    p = np.stack([rng.uniform(-5, -3, n) for _ in keys]).astype(np.float32)
+    slots = [o.slot(*k) for k in keys]
+    want_s, want_g = o.batch_grad(x, slots, p.astype(np.float64), "total_gaussian_surprise", dtype=32)
+    got_s, got_g = simd.batch(o, x, slots, p, "total_gaussian_surprise", gradient=True)
+    _bulk(_rel(got_s, want_s), "16-node logp")
+    for i in range(len(keys)):
+        _bulk(_rel(got_g[i], want_g[i], floor=1e-3 * np.abs(want_g[i]).max()), f"16-node gradient {keys[i]}")
+    assert np.array_equal(simd.batch(o, x, slots, p, None), np.zeros(n, dtype=np.float32))  # no response function: the filter alone
+
+
 def test_other_topologies_are_refused():
     o = nets.volatile2(onet.Network).create_belief_propagation_fn()
     with pytest.raises(NotImplementedError):
