@@ -352,7 +352,7 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
   // the reverse sweep (hgf_call_t::gradient_mode): a plain logp + gradient call on a topology that has one
   if (want_grad && c->gradient_mode != 1) {
     const bool plain = !c->trajectories && !c->surprise_pointwise && !c->last_attributes && c->world_size <= 1 && !c->generative &&
-                       !plan->prog.n_branches && c->response_fn != RESP_NONE;
+                       !plan->prog.n_branches && c->response_fn != RESP_NONE && plan->prog.n_fed == plan->prog.n_inputs;
     const bool available = plan->variant->reverse != nullptr && plain;
     if (c->gradient_mode == 2 && !available)
       return fail("gradient_mode = reverse: %s", plan->variant->reverse ? "the call asks for outputs only the forward-mode kernels produce"

@@ -471,22 +471,23 @@ class Network:
         return sub, local
 
     def specialise(self, gradient_parameters: int = 0, response_parameter: bool = False, float64: bool = False,
-                   verbose: bool = False) -> str:
+                   verbose: bool = False, reverse: bool = False) -> str:
         """Build (once per topology, cached on disk) and register register-resident kernels for THIS network's
         topology, so that it does not run through the opcode interpreter (``pyhgf_b200/specialise.py``).  The plain
         filter is always instantiated; ``gradient_parameters = k`` adds the logp+grad kernel for k filter parameters
         per pass (<= 4), ``response_parameter`` the variant that also differentiates one response-function parameter.
+        ``reverse=True`` also builds the topology's generated reverse sweep (one launch for any number of parameters).
         Returns the kernel name the network's plans report afterwards."""
         from . import specialise as sp
 
         if self._vector_nodes():  # the scan runs the implied network: that is the topology to specialise
             if self.scan_fn is None:
                 self.create_belief_propagation_fn()
-            return self._implied_network()[0].specialise(gradient_parameters, response_parameter, float64, verbose)
+            return self._implied_network()[0].specialise(gradient_parameters, response_parameter, float64, verbose, reverse)
         kernels = [(0, 0)]
         if gradient_parameters or response_parameter:
             kernels.append((min(int(gradient_parameters), 4), 1 if response_parameter else 0))
-        return sp.specialise(self, float32=() if float64 else kernels, float64=kernels if float64 else (), verbose=verbose)
+        return sp.specialise(self, float32=() if float64 else kernels, float64=kernels if float64 else (), verbose=verbose, reverse=reverse)
 
     # ----------------------------------------------------------------- inputs
     @property

@@ -46,7 +46,7 @@ def header_for(network, salt: str = "") -> tuple:
 
 
 def specialise(network, float32: Iterable[Sequence[int]] = ((0, 0),), float64: Iterable[Sequence[int]] = (),
-               verbose: bool = False, extra_flags: Sequence[str] = (), load: bool = True) -> str:
+               verbose: bool = False, extra_flags: Sequence[str] = (), load: bool = True, reverse: bool = False) -> str:
     """Build (or load from the cache) and register the specialisation of ``network``'s topology.
 
     float32 / float64 : the kernels to instantiate, as ``(PF, PR)`` pairs -- PF filter-parameter tangent
@@ -55,6 +55,9 @@ def specialise(network, float32: Iterable[Sequence[int]] = ((0, 0),), float64: I
     extra_flags : further nvcc flags for the kernel translation units (e.g. a math policy, ``-DHGF_EXP_MODE=2``:
         tools/parity_ablation.py builds one object per policy this way).
     load : False only builds the object (no GPU or loaded library needed: the CPU box pre-builds what the GPU box runs).
+    reverse : also generate and compile the topology's checkpointed reverse sweep (``revgen.py``; float32 and float64), so
+        that ``gradient=True`` with many parameters / ``gradient="reverse"`` costs one launch whatever their number.  Raises
+        ``revgen.Unsupported`` for node kinds / update schemes the generator does not restate.
     Returns the kernel name the network's plans will report (``"specialised:<hash>"``).
     """
     extra_flags = [str(f) for f in extra_flags]
@@ -65,11 +68,16 @@ def specialise(network, float32: Iterable[Sequence[int]] = ((0, 0),), float64: I
         if not (0 <= pf <= 4 and pr in (0, 1)):
             raise ValueError("kernels are (PF, PR) with 0 <= PF <= 4 and PR in (0, 1)")
     # content tag: kernels, math policy, every source the objects are compiled from (no paths: the cache travels)
-    tag = hashlib.sha1(repr((f32, f64, build.MATH, _source_hash(), header, extra_flags)).encode()).hexdigest()[:12]
+    rev_header = None
+    if reverse:
+        from . import revgen
+
+        rev_header = revgen.generate(name, network, network.volatility_updates, network.mean_field_updates, inputs=tuple(network.input_idxs))
+    tag = hashlib.sha1(repr((f32, f64, build.MATH, _source_hash(), header, extra_flags, rev_header)).encode()).hexdigest()[:12]
     so = os.path.join(OUT_DIR, f"libhgf_{name}_{tag}.so")
     label = f"specialised:{name}"
     if not os.path.exists(so):
-        _compile(name, header, f32, f64, so, label, verbose, extra_flags)
+        _compile(name, header, f32, f64, so, label, verbose, extra_flags, rev_header)
     if not load:
         return label
     L = _lib.lib()
@@ -83,12 +91,12 @@ def specialise(network, float32: Iterable[Sequence[int]] = ((0, 0),), float64: I
 
 def _source_hash() -> str:
     h = hashlib.sha1()
-    for path in build._headers() + [os.path.join(build.CSRC, f) for f in ("hgf_static_inst.cu", "hgf_specialisation.cu")]:
+    for path in build._headers() + [os.path.join(build.CSRC, f) for f in ("hgf_static_inst.cu", "hgf_specialisation.cu", "hgf_reverse_inst.cu")]:
         h.update(open(path, "rb").read())
     return h.hexdigest()
 
 
-def _compile(name, header, f32, f64, so, label, verbose, extra_flags=()):
+def _compile(name, header, f32, f64, so, label, verbose, extra_flags=(), rev_header=None):
     work = os.path.join(WORK_DIR, name)
     os.makedirs(work, exist_ok=True)
     os.makedirs(OUT_DIR, exist_ok=True)
@@ -102,8 +110,15 @@ def _compile(name, header, f32, f64, so, label, verbose, extra_flags=()):
                          topo_flags + [f"-DHGF_BASE={base}", f"-DHGF_NTAN={pf}", f"-DHGF_NRESP={pr}"] + list(extra_flags)))
     m32 = sum(_variant_bit(pf, pr) for pf, pr in f32)
     m64 = sum(_variant_bit(pf, pr) for pf, pr in f64)
+    rev_flags = []
+    if rev_header is not None:
+        with open(os.path.join(work, f"reverse_{name}.h"), "w") as f:
+            f.write(rev_header)
+        rev_flags = [f"-DHGF_REV_FN=reverse_{name}"]
+        jobs.append((os.path.join(build.CSRC, "hgf_reverse_inst.cu"), os.path.join(work, "reverse.o"),
+                     ["-I", work, f"-DHGF_REV_HEADER=<reverse_{name}.h>", f"-DHGF_REV_TYPE=Rev_{name}"] + rev_flags + list(extra_flags)))
     jobs.append((os.path.join(build.CSRC, "hgf_specialisation.cu"), os.path.join(work, "table.o"),
-                 topo_flags + [f'-DHGF_TOPO_LABEL="{label}"', f"-DHGF_MASK32={m32}u", f"-DHGF_MASK64={m64}u"]))
+                 topo_flags + [f'-DHGF_TOPO_LABEL="{label}"', f"-DHGF_MASK32={m32}u", f"-DHGF_MASK64={m64}u"] + rev_flags))
 
     def run(job):
         src, obj, flags = job
