@@ -302,7 +302,7 @@ def _child_gain_precision(op, L, child):  # posterior_update_mean_continuous_nod
     return pi_hat
 
 
-def posterior_continuous(op, L, node, dt, log_dt, cap, exact_sigmoid):  # continuous_node_posterior_update.py:20-128
+def _posterior_precision(op, L, node, dt, ehgf):  # posterior_update_precision_continuous_node.py:208-365 (eHGF form :627-750)
     t, e = op.tr, L.edges[node]
     obs = [op.field(c, "observed", diff=False) for c in list(_vc(e)) + list(_volc(e))]
     any_observed = " || ".join(f"({o.name} != F(0))" for o in obs)
@@ -320,14 +320,29 @@ def posterior_continuous(op, L, node, dt, log_dt, cap, exact_sigmoid):  # contin
     from_vol = t.lift(0.0)
     for k, c in enumerate(_volc(e)):
         kappa = op.get(L.cvolc(node, k))
-        gamma, vope = op.field(c, "temp.effective_precision"), op.field(c, "temp.volatility_prediction_error")
-        kg = kappa * gamma
-        from_vol = from_vol + (0.5 * (kg * kg) + (kg * kg) * vope - 0.5 * (kappa * kappa) * gamma * vope) * op.field(c, "observed", diff=False)
+        if ehgf:  # the volatility increment re-predicted from the node's NEW mean, :564-624
+            prev_var = op.field(c, "temp.current_variance")
+            omega = dt * t.exp(kappa * op.field(node, "mean") + op.field(c, "tonic_volatility"))
+            pi_hat = 1.0 / (prev_var + omega)
+            gamma = omega * pi_hat
+            weight = (omega - prev_var) * pi_hat
+            delta = op.field(c, "mean") - op.field(c, "expected_mean")
+            vope = (1.0 / op.field(c, "precision") + delta * delta) * pi_hat - 1.0
+            inc = t.cmax(0.0, 0.5 * (kappa * kappa) * gamma * (gamma + weight * vope))
+            from_vol = from_vol + inc * op.field(c, "observed", diff=False)
+        else:
+            gamma, vope = op.field(c, "temp.effective_precision"), op.field(c, "temp.volatility_prediction_error")
+            kg = kappa * gamma
+            from_vol = from_vol + (0.5 * (kg * kg) + (kg * kg) * vope - 0.5 * (kappa * kappa) * gamma * vope) * op.field(c, "observed", diff=False)
     observed = _nan_unless_positive(t, op.field(node, "expected_precision") + (from_values + from_vol))
-    pi = t.min_c(t.select(any_observed, observed, aged), cap)
-    op.put(node, "precision", pi)
+    return t.select(any_observed, observed, aged)
+
+
+def _posterior_mean(op, L, node, pi):  # posterior_update_mean_continuous_node.py:10-195
+    t, e = op.tr, L.edges[node]
     fv, fvol = t.lift(0.0), t.lift(0.0)
     for k, c in enumerate(_vc(e)):
+        _linear_only(L.edges, node, c)
         psi = op.get(L.cvc(node, k))
         vape = op.field(c, "temp.value_prediction_error") * op.field(c, "observed", diff=False)
         fv = fv + ((psi * _child_gain_precision(op, L, c)) / pi) * vape
@@ -335,7 +350,20 @@ def posterior_continuous(op, L, node, dt, log_dt, cap, exact_sigmoid):  # contin
         w = op.get(L.cvolc(node, k)) * op.field(c, "temp.effective_precision") * op.field(c, "temp.volatility_prediction_error")
         w = w * (1.0 / (2.0 * pi))
         fvol = fvol + w * op.field(c, "observed", diff=False)
-    op.put(node, "mean", op.field(node, "expected_mean") + fv + fvol)
+    return op.field(node, "expected_mean") + fv + fvol
+
+
+def posterior_continuous(op, L, node, dt, log_dt, cap, exact_sigmoid):  # continuous_node_posterior_update.py:20-128: precision, then mean
+    pi = op.tr.min_c(_posterior_precision(op, L, node, dt, False), cap)
+    op.put(node, "precision", pi)
+    op.put(node, "mean", _posterior_mean(op, L, node, pi))
+
+
+def posterior_continuous_ehgf(op, L, node, dt, log_dt, cap, exact_sigmoid):
+    """continuous_node_posterior_update_ehgf.py:20-155: the mean first (with the EXPECTED precision), then the precision
+    re-predicted from that mean."""
+    op.put(node, "mean", _posterior_mean(op, L, node, op.field(node, "expected_precision")))
+    op.put(node, "precision", op.tr.min_c(_posterior_precision(op, L, node, dt, True), cap))
 
 
 def _unbounded_mixture(t, explicit, prev_variance, c_precision, c_mean, c_expected_mean, c_expected_precision, mu_hat, pi_hat, kappa, omega,
@@ -459,10 +487,28 @@ def pe_volatile(op, L, node, dt, log_dt, cap, exact_sigmoid):  # prediction_erro
     vope = pi_hat / precision + pi_hat * (delta * delta) - 1.0
     op.put(node, "temp.value_prediction_error", delta)
     op.put(node, "temp.volatility_prediction_error", vope)
-    pi, mu = _unbounded_mixture(t, False, op.field(node, "temp.current_variance"), precision, mean, mu_hat, pi_hat,
-                                op.field(node, "expected_mean_vol"), op.field(node, "expected_precision_vol"), None, None, log_dt)
-    op.put(node, "precision_vol", t.min_c(pi, cap))
-    op.put(node, "mean_vol", mu)
+    if L.vol_updates == "unbounded":  # volatile_node_posterior_update_unbounded.py:12-178
+        pi, mu = _unbounded_mixture(t, False, op.field(node, "temp.current_variance"), precision, mean, mu_hat, pi_hat,
+                                    op.field(node, "expected_mean_vol"), op.field(node, "expected_precision_vol"), None, None, log_dt)
+        op.put(node, "precision_vol", t.min_c(pi, cap))
+        op.put(node, "mean_vol", mu)
+    elif L.vol_updates == "eHGF":  # volatile_node_posterior_update_ehgf.py:16-75 + posterior_update_volatility_level.py
+        gamma = op.field(node, "temp.effective_precision")
+        mean_vol = op.field(node, "expected_mean_vol") + (gamma * vope) / (2.0 * op.field(node, "expected_precision_vol"))
+        op.put(node, "mean_vol", mean_vol)
+        prev_var = op.field(node, "temp.current_variance")
+        omega = dt * t.exp(mean_vol)
+        pi_rep = 1.0 / (prev_var + omega)
+        gamma_rep = omega * pi_rep
+        weight = (omega - prev_var) * pi_rep
+        vope_rep = (1.0 / precision + delta * delta) * pi_rep - 1.0
+        inc = t.cmax(0.0, 0.5 * gamma_rep * (gamma_rep + weight * vope_rep))
+        op.put(node, "precision_vol", t.min_c(op.field(node, "expected_precision_vol") + inc, cap))
+    else:  # standard, volatile_node_posterior_update.py:75-107
+        gamma = op.field(node, "temp.effective_precision")
+        pi_vol = t.min_c(op.field(node, "expected_precision_vol") + (0.5 * (gamma * gamma) + (gamma * gamma) * vope - 0.5 * gamma * vope), cap)
+        op.put(node, "precision_vol", pi_vol)
+        op.put(node, "mean_vol", op.field(node, "expected_mean_vol") + (gamma * vope) / (2.0 * pi_vol))
 
 
 def posterior_volatile(op, L, node, dt, log_dt, cap, exact_sigmoid):  # posterior/volatile/posterior_update_value_level.py:11-245
@@ -485,6 +531,7 @@ OPS = {
     _lib.OPS["PRED_BINARY"]: predict_binary, _lib.OPS["PRED_CONT"]: predict_continuous,
     _lib.OPS["PE_BINARY"]: pe_binary, _lib.OPS["PE_CONT"]: pe_continuous,
     _lib.OPS["POST_CONT"]: posterior_continuous, _lib.OPS["POST_CONT_UNBOUNDED"]: posterior_continuous_unbounded,
+    _lib.OPS["POST_CONT_EHGF"]: posterior_continuous_ehgf,
     _lib.OPS["PRED_VOLATILE"]: predict_volatile, _lib.OPS["PE_VOLATILE"]: pe_volatile, _lib.OPS["POST_VOLATILE"]: posterior_volatile,
 }
 
@@ -592,11 +639,12 @@ def generate(name, network_like, vol_updates="unbounded", mean_field=False, inpu
     """The ``Rev_<name>`` struct of a network (anything with ``.edges``); raises Unsupported for node kinds / update
     schemes outside the generated set (then the library keeps to its forward-mode passes)."""
     edges = network_like.edges
-    if vol_updates != "unbounded" or mean_field:
-        raise Unsupported("the generated reverse sweep covers the default scheme (unbounded, relaxed)")
+    if mean_field:
+        raise Unsupported("the generated reverse sweep covers the relaxed (not the mean-field) scheme")
     if any(e.node_type not in (1, 2, 6) for e in edges):
         raise Unsupported("the generated reverse sweep covers binary, continuous and volatile state nodes")
     L = Layout(edges)
+    L.vol_updates = vol_updates
     pred, upd = get_update_sequence(network_like, vol_updates, mean_field)
     if inputs is None:
         inputs = tuple(i for i, e in enumerate(edges) if e.value_children is None and e.volatility_children is None)

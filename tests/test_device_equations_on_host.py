@@ -141,3 +141,18 @@ def test_generated_reverse_sweep_of_the_16_node_network(box):
             assert np.array_equal(logp, want_s), rname
             for i, k in enumerate(keys):
                 assert np.allclose(grad[i], want_g[i], rtol=1e-9, atol=1e-10 * max(np.abs(want_g[i]).max(), 1e-300)), (rname, k)
+
+
+@pytest.mark.parametrize("case", ["continuous3/eHGF", "continuous3/standard", "volatile2/eHGF", "volatile2/standard", "volatile2/unbounded",
+                                  "multi_child/eHGF", "multi_child/standard", "multi_child/unbounded"])
+def test_generated_reverse_sweep_covers_every_update_scheme(case):
+    """The sweep of a topology under each of the reference's three volatility-update schemes (unbounded / eHGF / standard;
+    get_update_sequence.py:176-222), generated and compiled for the host on the spot (tools/hostsim/revcheck.py): a
+    volatile-state node, a continuous HGF, and a user topology with two inputs, couplings among the parameters and irregular
+    time steps.  logp is the float64 oracle's bit for bit, every gradient the Dual<double> oracle's to 1e-10."""
+    import revcheck
+
+    cases = revcheck.CASES or revcheck._cases()
+    equal, worst = revcheck.compare(**cases[case])
+    assert equal
+    assert worst < 1e-10, worst

@@ -919,10 +919,12 @@ def test_on_demand_specialisation_matches_the_interpreter(G, R, build, monkeypat
         assert torch.allclose(a.trajectories[k], b.trajectories[k], rtol=RTOL_TRAJ, atol=1e-6, equal_nan=True), k
 
 
-def test_on_demand_specialisation_with_reverse_sweep(G, R):
+@pytest.mark.parametrize("scheme", ["unbounded", "eHGF"])
+def test_on_demand_specialisation_with_reverse_sweep(G, R, scheme):
     """A USER topology (two inputs under a shared value parent, itself under a value parent and a two-level volatility
     chain) specialised with `reverse=True`: the sweep generated and compiled on demand gives the Dual<double> oracle's
-    gradient wrt 7 parameters in one launch; a scheme the generator does not restate is refused, not mis-differentiated."""
+    gradient wrt 7 parameters in one launch; a scheme the generator does not restate (mean-field) is refused, not
+    mis-differentiated."""
     from pyhgf_b200 import _lib, revgen
 
     x = nets.ar1_series(200, n_series=2)
@@ -931,19 +933,22 @@ def test_on_demand_specialisation_with_reverse_sweep(G, R):
             (4, "volatility_coupling_children", 0), (3, "mean")]
     vals = [_grid(n, -4, -2, 1), _grid(n, -6, -4, 2), _grid(n, -4, -2, 3), _grid(n, -5, -3, 4), _grid(n, 0.5, 0.9, 5), _grid(n, 0.8, 1.2, 6),
             _grid(n, -0.3, 0.3, 7)]
-    net = nets.multi_child(G.Network, dtype="float64")
+    net = nets.multi_child(G.Network, dtype="float64", volatility_updates=scheme)
     name = net.specialise(float64=True, reverse=True)
     assert name.startswith("specialised:") and net.plan.kernel_name == name
     before = _lib.launch_count()
     res = net.batch(x, dict(zip(keys, vals)), response_function=R.total_gaussian_surprise, gradient=True)
     assert res.kernel_name == name and _lib.launch_count() - before == 1
-    o = nets.multi_child(onet.Network, dtype="float64").create_belief_propagation_fn()
+    o = nets.multi_child(onet.Network, dtype="float64", volatility_updates=scheme).create_belief_propagation_fn()
     want_s, want_g = o.batch_grad(x, [o.slot(*k) for k in keys], np.stack(vals), "total_gaussian_surprise")
-    assert np.allclose(res.surprise.cpu().numpy(), want_s, rtol=1e-9)
+    got_s = res.surprise.cpu().numpy()
+    ok = np.isfinite(want_s)  # (under the eHGF a few of these filters blow up: +inf surprise on both sides, no gradient to compare)
+    assert ok.sum() > n // 2 and np.array_equal(np.isfinite(got_s), ok)
+    assert np.allclose(got_s[ok], want_s[ok], rtol=1e-9)
     for i, k in enumerate(keys):
-        assert np.allclose(res.gradient[k].cpu().numpy(), want_g[i], rtol=1e-7, atol=1e-7 * np.abs(want_g[i]).max()), k
+        assert np.allclose(res.gradient[k].cpu().numpy()[ok], want_g[i][ok], rtol=1e-7, atol=1e-7 * np.abs(want_g[i][ok]).max()), k
     with pytest.raises(revgen.Unsupported):
-        nets.multi_child(G.Network, volatility_updates="eHGF").specialise(reverse=True)
+        nets.multi_child(G.Network, mean_field_updates=True).specialise(reverse=True)
 
 
 def test_generative_rollouts(G, datasets):
