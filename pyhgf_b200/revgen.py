@@ -6,7 +6,9 @@ Here the adjoint of ONE time step is written out ahead of time, as straight-line
 
   * the update equations of hgf_ops.cuh are restated below on TRACED scalars, one function per opcode, in the same
     operation order (each cites the reference it follows); running the network's schedule on them yields, per scheduled
-    operation, an SSA list of primitives (+, -, *, /, exp, log, sigmoid, logaddexp, lambert_w0, pow, select);
+    operation, an SSA list of primitives (+, -, *, /, exp, log, sigmoid, tanh, sin, cos, erf, logaddexp, lambert_w0, pow,
+    select).  Covered: binary, continuous and volatile-state nodes; the unbounded, eHGF and standard volatility updates and
+    their mean-field variants; every value-coupling function; every response function;
   * for every operation the generator emits (a) its forward code, which also logs the previous value of every attribute
     slot it overwrites, and (b) its reverse code: restore those slots, recompute the operation's SSA values (so that only
     ONE operation's intermediates are ever live, in registers) and run the adjoint statements in reverse order,
@@ -107,6 +109,10 @@ class Tracer:
     def sigmoid(self, x, exact=False):
         fwd = f"exact_rcp(F(1) + b_exp(-{x.name}))" if exact else f"b_rcp(F(1) + b_exp(-{x.name}))"
         return self.emit(fwd, [(x, "{g} * {r} * (F(1) - {r})")])
+    def tanh(self, x): return self.emit(f"b_tanh({x.name})", [(x, "{g} * (F(1) - {r} * {r})")])
+    def sin(self, x): return self.emit(f"b_sin({x.name})", [(x, "{g} * b_cos({a})")])
+    def cos(self, x): return self.emit(f"b_cos({x.name})", [(x, "-{g} * b_sin({a})")])
+    def erf(self, x): return self.emit(f"b_erf({x.name})", [(x, "{g} * F(1.1283791670955126) * b_exp(-{a} * {a})")])
     def lambert_w0(self, z): return self.emit(f"b_lambert_w0<F>({z.name})", [(z, "{g} * t_rcp(b_exp({r}) * (F(1) + {r}))")])
     def logaddexp(self, a, b):
         # jnp.logaddexp VJP: weights exp(a - out), exp(b - out) = the larger argument's 1 / (1 + e), the smaller one's e / (1 + e)
@@ -191,14 +197,70 @@ def _vc(e): return e.value_children or ()
 def _volc(e): return e.volatility_children or ()
 
 
-def _linear_only(edges, parent, child):
+def _coupling_fn(edges, parent, child) -> int:
+    """The coupling function (hgf_coupling_fn) of the value edge parent -> child (stored on the parent, add_edges.py)."""
+    from .topology import resolve_coupling_fn
+
     e = edges[parent]
     k = e.value_children.index(child)
     fn = e.coupling_fn[k] if (e.coupling_fn is not None and k < len(e.coupling_fn)) else None
-    from .topology import resolve_coupling_fn
+    return resolve_coupling_fn(fn)
 
-    if resolve_coupling_fn(fn) != 0:
-        raise Unsupported("the generated reverse sweep covers linear value couplings")
+
+CF = _lib.COUPLING_FNS
+
+
+# g, g', g'' of hgf_ops.cuh (cf_value / cf_prime / cf_second) on traced scalars: the tracer differentiates them like any
+# other composition of primitives (the reference applies jax.grad to the user's callable)
+def _cf_value(t, fn, x):
+    if fn == CF["relu"]:
+        return t.max_c(x, 0.0)
+    if fn == CF["sigmoid"]:
+        return t.sigmoid(x)
+    if fn == CF["tanh"]:
+        return t.tanh(x)
+    if fn == CF["leaky_relu"]:
+        return t.select(f"{x.name} >= F(0)", x, x * 0.01)
+    if fn == CF["gelu"]:
+        return x * 0.5 * (1.0 + t.erf(x / 1.4142135623730951))
+    if fn == CF["sin"]:
+        return t.sin(x)
+    return x
+
+
+def _cf_prime(t, fn, x):
+    if fn == CF["relu"]:
+        return t.select(f"{x.name} > F(0)", 1.0, 0.0)
+    if fn == CF["sigmoid"]:
+        g = t.sigmoid(x)
+        return g * (1.0 - g)
+    if fn == CF["tanh"]:
+        g = t.tanh(x)
+        return 1.0 - g * g
+    if fn == CF["leaky_relu"]:
+        return t.select(f"{x.name} >= F(0)", 1.0, 0.01)
+    if fn == CF["gelu"]:
+        cdf = 0.5 * (1.0 + t.erf(x / 1.4142135623730951))
+        pdf = t.exp(-(x * x) / 2.0) / 2.5066282746310002
+        return cdf + x * pdf
+    if fn == CF["sin"]:
+        return t.cos(x)
+    return t.lift(1.0)
+
+
+def _cf_second(t, fn, x):
+    if fn == CF["sigmoid"]:
+        g = t.sigmoid(x)
+        return g * (1.0 - g) * (1.0 - 2.0 * g)
+    if fn == CF["tanh"]:
+        g = t.tanh(x)
+        return -2.0 * g * (1.0 - g * g)
+    if fn == CF["gelu"]:
+        pdf = t.exp(-(x * x) / 2.0) / 2.5066282746310002
+        return pdf * (2.0 - x * x)
+    if fn == CF["sin"]:
+        return -t.sin(x)
+    return t.lift(0.0)
 
 
 def predict_binary(op, L, node, dt, log_dt, cap, exact_sigmoid):  # prediction/binary.py:12-93
@@ -220,8 +282,9 @@ def _predicted_mean(op, L, node, dt):  # prediction/continuous.py:11-103
         return lam * op.field(node, "mean") + dt * op.field(node, "tonic_drift")
     drift = op.field(node, "tonic_drift")
     for k, p in enumerate(_vp(e)):
-        _linear_only(L.edges, p, node)
-        drift = drift + op.get(L.cvp(node, k)) * op.field(p, "expected_mean")
+        fn = _coupling_fn(L.edges, p, node)
+        mu_par = op.field(p, "expected_mean")
+        drift = drift + op.get(L.cvp(node, k)) * (mu_par if fn == 0 else _cf_value(op.tr, fn, mu_par))
     return lam * op.field(node, "mean") + dt * drift
 
 
@@ -238,15 +301,18 @@ def predict_continuous(op, L, node, dt, log_dt, cap, exact_sigmoid):  # predicti
     for k, p in enumerate(_volp(e)):
         kappa = op.get(L.cvolp(node, k))
         log_vol = log_vol + kappa * op.field(p, "expected_mean")
-        log_vol = log_vol + (kappa * kappa) / (2.0 * op.field(p, "expected_precision"))
+        if not L.mean_field:  # the MGF term (prediction/continuous.py:207-231; mean-field :369-512 drops it and the Laplace term)
+            log_vol = log_vol + (kappa * kappa) / (2.0 * op.field(p, "expected_precision"))
     omega = _nan_unless_positive(t, dt * t.exp(log_vol))
     pi_cond = 1.0 / (variance + omega)
-    if not _vp(e):
+    if not _vp(e) or L.mean_field:
         pi_marg = pi_cond
     else:
         var = t.lift(0.0)
         for k, p in enumerate(_vp(e)):
-            c = dt * op.get(L.cvp(node, k))
+            fn = _coupling_fn(L.edges, p, node)
+            slope = t.lift(1.0) if fn == 0 else _cf_prime(t, fn, op.field(p, "expected_mean"))
+            c = dt * op.get(L.cvp(node, k)) * slope
             var = var + (c * c) / op.field(p, "expected_precision")
         pi_marg = 1.0 / (variance + omega + var)
     op.put(node, "temp.effective_precision", omega * pi_marg)
@@ -285,7 +351,7 @@ def _is_gaussian_interior(L, child):
 
 def _child_precision_weight(op, L, child):  # posterior_update_precision_continuous_node.py:41-80
     pi_hat = op.field(child, "expected_precision")
-    if _is_gaussian_interior(L, child):
+    if not L.mean_field and _is_gaussian_interior(L, child):
         pi_y = op.field(child, "precision") - pi_hat
         pi_c = op.field(child, "temp.conditional_expected_precision")
         return pi_c * pi_y / (pi_c + pi_y)
@@ -294,7 +360,7 @@ def _child_precision_weight(op, L, child):  # posterior_update_precision_continu
 
 def _child_gain_precision(op, L, child):  # posterior_update_mean_continuous_node.py:130-144
     pi_hat = op.field(child, "expected_precision")
-    if _is_gaussian_interior(L, child):
+    if not L.mean_field and _is_gaussian_interior(L, child):
         pi_child = op.field(child, "precision")
         pi_y = pi_child - pi_hat
         pi_c = op.field(child, "temp.conditional_expected_precision")
@@ -314,9 +380,14 @@ def _posterior_precision(op, L, node, dt, ehgf):  # posterior_update_precision_c
     aged = 1.0 / (1.0 / op.field(node, "precision") + dt * t.exp(log_vol))
     from_values = t.lift(0.0)
     for k, c in enumerate(_vc(e)):
-        _linear_only(L.edges, node, c)
+        fn = _coupling_fn(L.edges, node, c)
         psi = op.get(L.cvc(node, k))
-        from_values = from_values + _child_precision_weight(op, L, c) * (psi * psi) * op.field(c, "observed", diff=False)
+        if fn == 0:
+            curvature = psi * psi
+        else:  # posterior_update_precision_continuous_node.py:116-126, at the node's current mean
+            g1 = _cf_prime(t, fn, op.field(node, "mean"))
+            curvature = (psi * psi) * (g1 * g1) - psi * _cf_second(t, fn, op.field(node, "mean")) * op.field(c, "temp.value_prediction_error")
+        from_values = from_values + _child_precision_weight(op, L, c) * curvature * op.field(c, "observed", diff=False)
     from_vol = t.lift(0.0)
     for k, c in enumerate(_volc(e)):
         kappa = op.get(L.cvolc(node, k))
@@ -342,10 +413,13 @@ def _posterior_mean(op, L, node, pi):  # posterior_update_mean_continuous_node.p
     t, e = op.tr, L.edges[node]
     fv, fvol = t.lift(0.0), t.lift(0.0)
     for k, c in enumerate(_vc(e)):
-        _linear_only(L.edges, node, c)
+        fn = _coupling_fn(L.edges, node, c)
         psi = op.get(L.cvc(node, k))
         vape = op.field(c, "temp.value_prediction_error") * op.field(c, "observed", diff=False)
-        fv = fv + ((psi * _child_gain_precision(op, L, c)) / pi) * vape
+        if fn == 0:
+            fv = fv + ((psi * _child_gain_precision(op, L, c)) / pi) * vape
+        else:
+            fv = fv + ((psi * _child_gain_precision(op, L, c) * _cf_prime(t, fn, op.field(node, "mean"))) / pi) * vape
     for k, c in enumerate(_volc(e)):
         w = op.get(L.cvolc(node, k)) * op.field(c, "temp.effective_precision") * op.field(c, "temp.volatility_prediction_error")
         w = w * (1.0 / (2.0 * pi))
@@ -451,22 +525,25 @@ def predict_volatile(op, L, node, dt, log_dt, cap, exact_sigmoid):  # prediction
     op.put(node, "expected_mean_vol", mu_hat_vol)
     op.put(node, "expected_precision_vol", pi_hat_vol)
     op.put(node, "temp.effective_precision_vol", omega_vol * pi_hat_vol)
-    log_vol = mu_hat_vol + 1.0 / (2.0 * pi_hat_vol)
+    log_vol = mu_hat_vol if L.mean_field else mu_hat_vol + 1.0 / (2.0 * pi_hat_vol)
     omega = _nan_unless_positive(t, dt * t.exp(log_vol))
     pi_cond = 1.0 / (variance + omega)
-    if not _vp(e):
+    if not _vp(e) or L.mean_field:
         pi_marg = pi_cond
     else:
         var = t.lift(0.0)
         for k, p in enumerate(_vp(e)):
-            c = dt * op.get(L.cvp(node, k))
+            fn = _coupling_fn(L.edges, p, node)
+            slope = t.lift(1.0) if fn == 0 else _cf_prime(t, fn, op.field(p, "expected_mean"))
+            c = dt * op.get(L.cvp(node, k)) * slope
             var = var + (c * c) / op.field(p, "expected_precision")
         pi_marg = 1.0 / (variance + omega + var)
     lam = op.field(node, "autoconnection_strength")
     drift = t.lift(0.0)  # (a volatile node has no tonic drift, volatile.py:51-108)
     for k, p in enumerate(_vp(e)):
-        _linear_only(L.edges, p, node)
-        drift = drift + op.get(L.cvp(node, k)) * op.field(p, "expected_mean")
+        fn = _coupling_fn(L.edges, p, node)
+        mu_par = op.field(p, "expected_mean")
+        drift = drift + op.get(L.cvp(node, k)) * (mu_par if fn == 0 else _cf_value(t, fn, mu_par))
     op.put(node, "expected_mean", lam * op.field(node, "mean") + dt * drift)
     if not _vc(e) and not _volc(e) and not _volp(e):
         op.put(node, "expected_precision", op.field(node, "precision"))
@@ -516,14 +593,25 @@ def posterior_volatile(op, L, node, dt, log_dt, cap, exact_sigmoid):  # posterio
     pi_hat = op.field(node, "expected_precision")
     pi = pi_hat
     for k, c in enumerate(_vc(e)):
-        _linear_only(L.edges, node, c)
+        fn = _coupling_fn(L.edges, node, c)
         psi = op.get(L.cvc(node, k))
-        pi = pi + (psi * psi) * _child_precision_weight(op, L, c)
+        w = _child_precision_weight(op, L, c)
+        if fn == 0:
+            pi = pi + (psi * psi) * w
+        else:  # coupling derivatives at the EXPECTED mean (posterior_update_value_level.py:120-125)
+            g1 = _cf_prime(t, fn, op.field(node, "expected_mean"))
+            g2 = _cf_second(t, fn, op.field(node, "expected_mean"))
+            pi = pi + w * ((psi * psi) * (g1 * g1) - psi * g2 * op.field(c, "temp.value_prediction_error"))
     pi = t.min_c(t.maximum(pi, pi_hat), cap)
     op.put(node, "precision", pi)
     gain = t.lift(0.0)
     for k, c in enumerate(_vc(e)):
-        gain = gain + ((op.get(L.cvc(node, k)) * _child_gain_precision(op, L, c)) / pi) * op.field(c, "temp.value_prediction_error")
+        fn = _coupling_fn(L.edges, node, c)
+        if fn == 0:
+            gain = gain + ((op.get(L.cvc(node, k)) * _child_gain_precision(op, L, c)) / pi) * op.field(c, "temp.value_prediction_error")
+        else:
+            slope = _cf_prime(t, fn, op.field(node, "expected_mean"))
+            gain = gain + ((op.get(L.cvc(node, k)) * _child_gain_precision(op, L, c) * slope) / pi) * op.field(c, "temp.value_prediction_error")
     op.put(node, "mean", op.field(node, "expected_mean") + gain)
 
 
@@ -532,6 +620,9 @@ OPS = {
     _lib.OPS["PE_BINARY"]: pe_binary, _lib.OPS["PE_CONT"]: pe_continuous,
     _lib.OPS["POST_CONT"]: posterior_continuous, _lib.OPS["POST_CONT_UNBOUNDED"]: posterior_continuous_unbounded,
     _lib.OPS["POST_CONT_EHGF"]: posterior_continuous_ehgf,
+    # the mean-field variants are the same functions with Layout.mean_field set (hgf_ops.cuh passes a flag the same way)
+    _lib.OPS["PRED_CONT_MF"]: predict_continuous, _lib.OPS["PRED_VOLATILE_MF"]: predict_volatile, _lib.OPS["POST_CONT_MF"]: posterior_continuous,
+    _lib.OPS["POST_CONT_EHGF_MF"]: posterior_continuous_ehgf, _lib.OPS["POST_VOLATILE_MF"]: posterior_volatile,
     _lib.OPS["PRED_VOLATILE"]: predict_volatile, _lib.OPS["PE_VOLATILE"]: pe_volatile, _lib.OPS["POST_VOLATILE"]: posterior_volatile,
 }
 
@@ -639,12 +730,10 @@ def generate(name, network_like, vol_updates="unbounded", mean_field=False, inpu
     """The ``Rev_<name>`` struct of a network (anything with ``.edges``); raises Unsupported for node kinds / update
     schemes outside the generated set (then the library keeps to its forward-mode passes)."""
     edges = network_like.edges
-    if mean_field:
-        raise Unsupported("the generated reverse sweep covers the relaxed (not the mean-field) scheme")
     if any(e.node_type not in (1, 2, 6) for e in edges):
         raise Unsupported("the generated reverse sweep covers binary, continuous and volatile state nodes")
     L = Layout(edges)
-    L.vol_updates = vol_updates
+    L.vol_updates, L.mean_field = vol_updates, bool(mean_field)
     pred, upd = get_update_sequence(network_like, vol_updates, mean_field)
     if inputs is None:
         inputs = tuple(i for i, e in enumerate(edges) if e.value_children is None and e.volatility_children is None)

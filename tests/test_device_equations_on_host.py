@@ -144,12 +144,18 @@ def test_generated_reverse_sweep_of_the_16_node_network(box):
 
 
 @pytest.mark.parametrize("case", ["continuous3/eHGF", "continuous3/standard", "volatile2/eHGF", "volatile2/standard", "volatile2/unbounded",
-                                  "multi_child/eHGF", "multi_child/standard", "multi_child/unbounded"])
+                                  "multi_child/eHGF", "multi_child/standard", "multi_child/unbounded",
+                                  "multi_child/unbounded+mean-field", "multi_child/eHGF+mean-field", "volatile2/unbounded+mean-field",
+                                  "continuous3/standard+mean-field",
+                                  "coupling/tanh-sin", "coupling/sigmoid-gelu", "coupling/relu-leaky_relu", "coupling/gelu-identity", "coupling/sin-tanh",
+                                  "coupling/volatile-tanh", "coupling/volatile-gelu"])
 def test_generated_reverse_sweep_covers_every_update_scheme(case):
     """The sweep of a topology under each of the reference's three volatility-update schemes (unbounded / eHGF / standard;
-    get_update_sequence.py:176-222), generated and compiled for the host on the spot (tools/hostsim/revcheck.py): a
-    volatile-state node, a continuous HGF, and a user topology with two inputs, couplings among the parameters and irregular
-    time steps.  logp is the float64 oracle's bit for bit, every gradient the Dual<double> oracle's to 1e-10."""
+    get_update_sequence.py:176-222), their mean-field variants, and every non-linear value-coupling function, generated and
+    compiled for the host on the spot (tools/hostsim/revcheck.py): a volatile-state node, a continuous HGF, a user topology with
+    two inputs, couplings among the parameters and irregular time steps, and chains with tanh / sin / sigmoid / gelu / relu /
+    leaky-relu / identity couplings under continuous and volatile-state parents.  logp is the float64 oracle's bit for bit, every
+    gradient the Dual<double> oracle's to 1e-10."""
     import revcheck
 
     cases = revcheck.CASES or revcheck._cases()

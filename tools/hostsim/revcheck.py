@@ -100,6 +100,31 @@ def _cases():
                                          (2, "value_coupling_children", 1), (4, "volatility_coupling_children", 0)],
             values=[rng.uniform(-5, -4, n), rng.uniform(-6, -5, n), rng.uniform(-5, -4, n), rng.uniform(-6, -5, n), rng.uniform(0.5, 0.9, n), rng.uniform(0.8, 1.2, n)],
             series=x2, response="total_gaussian_surprise", time_steps=rng.uniform(0.8, 1.2, 150), volatility_updates=scheme)
+    for name in ("multi_child/unbounded", "multi_child/eHGF", "volatile2/unbounded", "continuous3/standard"):  # the mean-field variants
+        CASES[name + "+mean-field"] = dict(CASES[name], mean_field_updates=True)
+    # non-linear value couplings (the reference differentiates the user's callable; here g, g', g'' are restated on traced
+    # scalars and differentiated by the generator): every enum function, on a continuous parent, a second-level parent
+    # (interior Gaussian child) and a volatile-state parent
+    def chain(fn_low, fn_high):
+        return lambda cls, **kw: (cls(**kw).add_nodes(precision=10.0).add_nodes(value_children=0, coupling_fn=(fn_low,), tonic_volatility=-3.0)
+                                  .add_nodes(value_children=1, coupling_fn=(fn_high,), tonic_volatility=-4.0).add_nodes(volatility_children=1, tonic_volatility=-4.0))
+
+    def volatile_parent(fn):
+        return lambda cls, **kw: cls(**kw).add_nodes(precision=10.0).add_nodes(kind="volatile-state", value_children=0, coupling_fn=(fn,), autoconnection_strength=1.0)
+
+    xs = 0.5 * x1 + 0.2
+    for low, high in (("tanh", "sin"), ("sigmoid", "gelu"), ("relu", "leaky_relu"), ("gelu", "identity"), ("sin", "tanh")):
+        CASES[f"coupling/{low}-{high}"] = dict(
+            make=chain(low, high), keys=[(1, "tonic_volatility"), (2, "tonic_volatility"), (3, "tonic_volatility"), (1, "value_coupling_children", 0),
+                                         (2, "value_coupling_children", 0), (1, "mean"), (2, "mean")],
+            values=[rng.uniform(-4, -3, n), rng.uniform(-5, -4, n), rng.uniform(-5, -4, n), rng.uniform(0.8, 1.2, n), rng.uniform(0.8, 1.2, n),
+                    rng.uniform(0.1, 0.5, n), rng.uniform(0.1, 0.5, n)],
+            series=xs, response="first_level_gaussian_surprise", volatility_updates="eHGF" if low == "sin" else "unbounded")
+    for fn in ("tanh", "gelu"):
+        CASES[f"coupling/volatile-{fn}"] = dict(
+            make=volatile_parent(fn), keys=[(1, "tonic_volatility_vol"), (1, "mean"), (1, "value_coupling_children", 0), (1, "mean_vol")],
+            values=[rng.uniform(-5, -3, n), rng.uniform(0.1, 0.5, n), rng.uniform(0.8, 1.2, n), rng.uniform(-3, -1, n)],
+            series=xs, response="first_level_gaussian_surprise")
     return CASES
 
 
