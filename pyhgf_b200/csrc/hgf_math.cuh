@@ -67,25 +67,190 @@ namespace hgf {
 // ----------------------------------------------------------------------------
 // Dual numbers
 // ----------------------------------------------------------------------------
+// Tangent arithmetic uses fused multiply-adds explicitly (the primal's contraction is the compiler's: on in the
+// shipped build, off with -fmad=false in the validation build).
+HGF_HD float b_fma(float a, float b, float c) { return ::fmaf(a, b, c); }
+HGF_HD double b_fma(double a, double b, double c) { return ::fma(a, b, c); }
+
+// The tangent vector of a Dual.  Generic form: P scalars, every operation a loop over them.
+// PACKED form (float, P >= 2; HGF_PACKED_TANGENTS): the tangents live in 64-bit register PAIRS and every operation is one
+// Blackwell packed-FP32 instruction per pair -- fma / mul / add .rn.f32x2 (SASS FFMA2 / FMUL2 / FADD2), which take the scalar
+// multiplier as a broadcast operand.  Lane throughput is that of two scalar instructions (tools/ubench/pipes.cu), but it
+// is ONE issue slot, and the logp+grad kernels are issue-bound: the 3-level binary HGF with two filter tangents executes
+// 797 warp-instructions per instance-step unpacked, most of them tangent arithmetic on the FP32 pipe.  Same IEEE
+// operations in the same order as the generic form (an odd P pads the last pair with a lane that is never read).
+#ifndef HGF_PACKED_TANGENTS
+#define HGF_PACKED_TANGENTS 1
+#endif
+struct F2 { unsigned long long u; };  // two float32 {lo, hi}
+HGF_HD F2 f2_make(float lo, float hi) {
+  F2 r;
+#ifdef __CUDA_ARCH__
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.u) : "f"(lo), "f"(hi));
+#else
+  unsigned int a, b;
+  __builtin_memcpy(&a, &lo, 4); __builtin_memcpy(&b, &hi, 4);
+  r.u = static_cast<unsigned long long>(a) | (static_cast<unsigned long long>(b) << 32);
+#endif
+  return r;
+}
+HGF_HD float f2_lo(F2 x) {
+#ifdef __CUDA_ARCH__
+  float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x.u)); return lo;
+#else
+  const unsigned int a = static_cast<unsigned int>(x.u); float f; __builtin_memcpy(&f, &a, 4); return f;
+#endif
+}
+HGF_HD float f2_hi(F2 x) {
+#ifdef __CUDA_ARCH__
+  float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x.u)); return hi;
+#else
+  const unsigned int a = static_cast<unsigned int>(x.u >> 32); float f; __builtin_memcpy(&f, &a, 4); return f;
+#endif
+}
+HGF_HD F2 f2_add(F2 a, F2 b) {
+#ifdef __CUDA_ARCH__
+  F2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u)); return r;
+#else
+  return f2_make(f2_lo(a) + f2_lo(b), f2_hi(a) + f2_hi(b));
+#endif
+}
+HGF_HD F2 f2_sub(F2 a, F2 b) {
+#ifdef __CUDA_ARCH__
+  F2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u)); return r;
+#else
+  return f2_make(f2_lo(a) - f2_lo(b), f2_hi(a) - f2_hi(b));
+#endif
+}
+HGF_HD F2 f2_scale(F2 a, float s) {  // a * s
+#ifdef __CUDA_ARCH__
+  F2 r, b; asm("mov.b64 %0, {%1, %1};" : "=l"(b.u) : "f"(s)); asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u)); return r;
+#else
+  return f2_make(f2_lo(a) * s, f2_hi(a) * s);
+#endif
+}
+HGF_HD F2 f2_fma(F2 a, float s, F2 c) {  // fma(a, s, c)
+#ifdef __CUDA_ARCH__
+  F2 r, b; asm("mov.b64 %0, {%1, %1};" : "=l"(b.u) : "f"(s)); asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.u) : "l"(a.u), "l"(b.u), "l"(c.u)); return r;
+#else
+  return f2_make(::fmaf(f2_lo(a), s, f2_lo(c)), ::fmaf(f2_hi(a), s, f2_hi(c)));
+#endif
+}
+
+template <class B, int P> struct use_packed { static constexpr bool value = false; };
+#if HGF_PACKED_TANGENTS
+template <int P> struct use_packed<float, P> { static constexpr bool value = P >= 2; };
+#endif
+
+template <class B, int P, bool PACKED = use_packed<B, P>::value> struct Tan;
+template <class B, int P> struct Tan<B, P, false> {
+  B e[P > 0 ? P : 1];  // P = 0: the plain filter (the unused element is never touched and is optimised away)
+  HGF_HD B get(int i) const { return e[i]; }
+  HGF_HD void set(int i, B x) { e[i] = x; }
+  HGF_HD void zero() {
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = B(0);
+  }
+  HGF_HD void add(const Tan& a, const Tan& b) {  // a + b
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = a.e[i] + b.e[i];
+  }
+  HGF_HD void sub(const Tan& a, const Tan& b) {  // a - b
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = a.e[i] - b.e[i];
+  }
+  HGF_HD void neg(const Tan& a) {
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = -a.e[i];
+  }
+  HGF_HD void scale(const Tan& a, B s) {  // a * s
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = a.e[i] * s;
+  }
+  HGF_HD void product(const Tan& a, B bv, B av, const Tan& b) {  // fma(a, bv, av * b): the product rule
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = b_fma(a.e[i], bv, av * b.e[i]);
+  }
+  HGF_HD void quotient(B q, const Tan& b, const Tan& a, B inv) {  // fma(-q, b, a) * inv: the quotient rule
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = b_fma(-q, b.e[i], a.e[i]) * inv;
+  }
+  HGF_HD void blend(const Tan& a, B wa, const Tan& b, B wb) {  // fma(a, wa, b * wb)
+#pragma unroll
+    for (int i = 0; i < P; ++i) e[i] = b_fma(a.e[i], wa, b.e[i] * wb);
+  }
+  template <class T2> HGF_HD void widen_from(const T2& a, int n) {  // the first n tangents of a (the others keep their value)
+#pragma unroll
+    for (int i = 0; i < P; ++i)
+      if (i < n) e[i] = a.get(i);
+  }
+};
+template <int P> struct Tan<float, P, true> {
+  static constexpr int NP = (P + 1) / 2;
+  F2 e[NP];
+  HGF_HD float get(int i) const { return (i & 1) ? f2_hi(e[i >> 1]) : f2_lo(e[i >> 1]); }
+  HGF_HD void set(int i, float x) {
+    F2& p = e[i >> 1];
+    p = (i & 1) ? f2_make(f2_lo(p), x) : f2_make(x, f2_hi(p));
+  }
+  HGF_HD void zero() {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k].u = 0ull;
+  }
+  HGF_HD void add(const Tan& a, const Tan& b) {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k] = f2_add(a.e[k], b.e[k]);
+  }
+  HGF_HD void sub(const Tan& a, const Tan& b) {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k] = f2_sub(a.e[k], b.e[k]);
+  }
+  HGF_HD void neg(const Tan& a) {  // (a * -1: an exact sign flip, zeros included)
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k] = f2_scale(a.e[k], -1.0f);
+  }
+  HGF_HD void scale(const Tan& a, float s) {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k] = f2_scale(a.e[k], s);
+  }
+  HGF_HD void product(const Tan& a, float bv, float av, const Tan& b) {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k] = f2_fma(a.e[k], bv, f2_scale(b.e[k], av));
+  }
+  HGF_HD void quotient(float q, const Tan& b, const Tan& a, float inv) {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k] = f2_scale(f2_fma(b.e[k], -q, a.e[k]), inv);
+  }
+  HGF_HD void blend(const Tan& a, float wa, const Tan& b, float wb) {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) e[k] = f2_fma(a.e[k], wa, f2_scale(b.e[k], wb));
+  }
+  template <class T2> HGF_HD void widen_from(const T2& a, int n) {
+#pragma unroll
+    for (int i = 0; i < P; ++i)
+      if (i < n) set(i, a.get(i));
+  }
+  template <int P2> HGF_HD void widen_from(const Tan<float, P2, true>& a, int n) {  // whole pairs move as pairs
+    constexpr int NP2 = (P2 + 1) / 2;
+#pragma unroll
+    for (int k = 0; k < NP; ++k)
+      if (k < NP2 && 2 * k + 1 < n) e[k] = a.e[k];
+      else if (k < NP2 && 2 * k < n) e[k] = f2_make(f2_lo(a.e[k]), f2_hi(e[k]));
+  }
+};
+
 template <class B, int P>
 struct Dual {
   B v;
-  B d[P > 0 ? P : 1];  // P = 0: the plain filter (the unused element is never touched and is optimised away)
+  Tan<B, P> d;
   HGF_HD Dual() {}
-  HGF_HD Dual(B x) : v(x) {  // NOLINT(runtime/explicit)
-#pragma unroll
-    for (int i = 0; i < P; ++i) d[i] = B(0);
-  }
+  HGF_HD Dual(B x) : v(x) { d.zero(); }  // NOLINT(runtime/explicit)
 };
 
 template <class T> struct scalar_traits { using base = T; static constexpr int n_tangents = 0; };
 template <class B, int P> struct scalar_traits<Dual<B, P>> { using base = B; static constexpr int n_tangents = P; };
 template <class T> using base_t = typename scalar_traits<T>::base;
 
-// Tangent arithmetic uses fused multiply-adds explicitly (the primal's contraction is the compiler's: on in the
-// shipped build, off with -fmad=false in the validation build).
-HGF_HD float b_fma(float a, float b, float c) { return ::fmaf(a, b, c); }
-HGF_HD double b_fma(double a, double b, double c) { return ::fma(a, b, c); }
 
 #ifdef HGF_MATH_ACCURATE
 #undef HGF_DIV_MODE
@@ -248,26 +413,22 @@ template <class T> HGF_HD T lit(double c) { return T(static_cast<base_t<T>>(c));
 
 template <class B, int P> HGF_HD Dual<B, P> operator+(const Dual<B, P>& a, const Dual<B, P>& b) {
   Dual<B, P> r; r.v = a.v + b.v;
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = a.d[i] + b.d[i];
+  r.d.add(a.d, b.d);
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator-(const Dual<B, P>& a, const Dual<B, P>& b) {
   Dual<B, P> r; r.v = a.v - b.v;
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = a.d[i] - b.d[i];
+  r.d.sub(a.d, b.d);
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator-(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = -a.v;
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = -a.d[i];
+  r.d.neg(a.d);
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator*(const Dual<B, P>& a, const Dual<B, P>& b) {
   Dual<B, P> r; r.v = a.v * b.v;
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = b_fma(a.d[i], b.v, a.v * b.d[i]);
+  r.d.product(a.d, b.v, a.v, b.d);
   return r;
 }
 // a / b for the primal of a Dual, and the tangent-grade reciprocal of b for its derivative: with the SFU
@@ -288,10 +449,7 @@ template <class F> HGF_HD void dual_div_primal(double a, double b, double& q, bo
 }
 template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, const Dual<B, P>& b) {
   Dual<B, P> r;
-  dual_div_primal(a.v, b.v, r.v, P > 0, [&](B inv) {
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = b_fma(-r.v, b.d[i], a.d[i]) * inv;
-  });
+  dual_div_primal(a.v, b.v, r.v, P > 0, [&](B inv) { r.d.quotient(r.v, b.d, a.d, inv); });
   return r;
 }
 // a / b with the primal quotient at IEEE accuracy under every policy (see exact_div_from_rcp)
@@ -304,8 +462,7 @@ template <int P> HGF_HD Dual<float, P> exact_div(const Dual<float, P>& a, const 
   const float inv = t_rcp(b.v);
   r.v = a.v / b.v;
 #endif
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = b_fma(-r.v, b.d[i], a.d[i]) * inv;
+  r.d.quotient(r.v, b.d, a.d, inv);
   return r;
 }
 template <int P> HGF_HD Dual<double, P> exact_div(const Dual<double, P>& a, const Dual<double, P>& b) { return a / b; }
@@ -316,26 +473,18 @@ template <class B, int P> HGF_HD Dual<B, P> operator-(const Dual<B, P>& a, B b) 
 template <class B, int P> HGF_HD Dual<B, P> operator-(B a, const Dual<B, P>& b) { Dual<B, P> r = -b; r.v = a - b.v; return r; }
 template <class B, int P> HGF_HD Dual<B, P> operator*(const Dual<B, P>& a, B b) {
   Dual<B, P> r; r.v = a.v * b;
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * b;
+  r.d.scale(a.d, b);
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator*(B a, const Dual<B, P>& b) { return b * a; }
 template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, B b) {
   Dual<B, P> r;
-  dual_div_primal(a.v, b, r.v, P > 0, [&](B inv) {
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
-  });
+  dual_div_primal(a.v, b, r.v, P > 0, [&](B inv) { r.d.scale(a.d, inv); });
   return r;
 }
 template <class B, int P> HGF_HD Dual<B, P> operator/(B a, const Dual<B, P>& b) {
   Dual<B, P> r;
-  dual_div_primal(a, b.v, r.v, P > 0, [&](B inv) {
-    const B c = -r.v * inv;
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = c * b.d[i];
-  });
+  dual_div_primal(a, b.v, r.v, P > 0, [&](B inv) { r.d.scale(b.d, -r.v * inv); });
   return r;
 }
 
@@ -423,47 +572,58 @@ HGF_D double x_pow(double x, double y) { return b_pow(x, y); }
 
 template <class B, int P> HGF_D Dual<B, P> x_exp(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_exp(a.v);
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = r.v * a.d[i];
+  r.d.scale(a.d, r.v);
+  return r;
+}
+// exp(-x) with the negation folded into the tangent's scale factor (same values as x_exp(-x), one instruction less per
+// tangent pair), and x * x with the product rule collapsed to 2 x dx
+HGF_D float x_exp_neg(float x) { return b_exp(-x); }
+HGF_D double x_exp_neg(double x) { return b_exp(-x); }
+template <class B, int P> HGF_D Dual<B, P> x_exp_neg(const Dual<B, P>& a) {
+  Dual<B, P> r; r.v = b_exp(-a.v);
+  r.d.scale(a.d, -r.v);
+  return r;
+}
+HGF_HD float x_square(float x) { return x * x; }
+HGF_HD double x_square(double x) { return x * x; }
+template <class B, int P> HGF_HD Dual<B, P> x_square(const Dual<B, P>& a) {
+  Dual<B, P> r; r.v = a.v * a.v;
+  r.d.scale(a.d, a.v + a.v);
   return r;
 }
 template <class B, int P> HGF_D Dual<B, P> x_log(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_log(a.v);
   if constexpr (P > 0) {
     const B inv = t_rcp(a.v);
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = a.d[i] * inv;
+    r.d.scale(a.d, inv);
   }
   return r;
 }
 template <class B, int P> HGF_D Dual<B, P> x_sin(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_sin(a.v); const B c = b_cos(a.v);
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = c * a.d[i];
+  r.d.scale(a.d, c);
   return r;
 }
 template <class B, int P> HGF_D Dual<B, P> x_cos(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_cos(a.v); const B s = -b_sin(a.v);
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = s * a.d[i];
+  r.d.scale(a.d, s);
   return r;
 }
 template <class B, int P> HGF_D Dual<B, P> x_tanh(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_tanh(a.v); const B c = B(1) - r.v * r.v;
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = c * a.d[i];
+  r.d.scale(a.d, c);
   return r;
 }
 template <class B, int P> HGF_D Dual<B, P> x_erf(const Dual<B, P>& a) {
   Dual<B, P> r; r.v = b_erf(a.v);
   const B c = B(1.1283791670955126) * b_exp(-a.v * a.v);
-#pragma unroll
-  for (int i = 0; i < P; ++i) r.d[i] = c * a.d[i];
+  r.d.scale(a.d, c);
   return r;
 }
 // jnp.power JVP given the primal r = x^y: y x^(y-1) dx + log(x) x^y dy
 template <class B, int P> HGF_D Dual<B, P> pow_with_primal(B primal, const Dual<B, P>& a, const Dual<B, P>& b) {
   Dual<B, P> r; r.v = primal;
+  r.d.zero();
   if constexpr (P > 0) {
 #ifdef HGF_SFU_TANGENTS
     const B da = b.v * r.v * t_rcp(a.v);
@@ -472,10 +632,10 @@ template <class B, int P> HGF_D Dual<B, P> pow_with_primal(B primal, const Dual<
 #endif
     const B db = b_log(a.v) * r.v;
 #pragma unroll
-    for (int i = 0; i < P; ++i) {
-      B t = da * a.d[i];
-      if (b.d[i] != B(0)) t = b_fma(db, b.d[i], t);
-      r.d[i] = t;
+    for (int i = 0; i < P; ++i) {  // (element by element: the log term only where dy != 0)
+      B t = da * a.d.get(i);
+      if (b.d.get(i) != B(0)) t = b_fma(db, b.d.get(i), t);
+      r.d.set(i, t);
     }
   }
   return r;
@@ -520,8 +680,7 @@ template <class B, int P> HGF_D Dual<B, P> x_sigmoid(const Dual<B, P>& x) {
   r.v = b_rcp(B(1) + b_exp(-x.v));
   if constexpr (P > 0) {
     const B c = r.v * (B(1) - r.v);
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = c * x.d[i];
+    r.d.scale(x.d, c);
   }
   return r;
 }
@@ -533,8 +692,7 @@ template <class B, int P> HGF_D Dual<B, P> x_sigmoid_exact(const Dual<B, P>& x) 
   r.v = exact_rcp(B(1) + b_exp(-x.v));
   if constexpr (P > 0) {
     const B c = r.v * (B(1) - r.v);
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = c * x.d[i];
+    r.d.scale(x.d, c);
   }
   return r;
 }
@@ -559,8 +717,7 @@ template <class B, int P> HGF_D Dual<B, P> x_logaddexp(const Dual<B, P>& a, cons
     const B w_hi = t_rcp(B(1) + e), w_lo = B(1) - w_hi;
     const bool a_hi = a.v >= b.v;
     const B wa = a_hi ? w_hi : w_lo, wb = a_hi ? w_lo : w_hi;
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = b_fma(a.d[i], wa, b.d[i] * wb);
+    r.d.blend(a.d, wa, b.d, wb);
   }
   return r;
 }
@@ -585,8 +742,7 @@ template <class B, int P> HGF_D Dual<B, P> x_lambert_w0(const Dual<B, P>& z) {
   Dual<B, P> r; r.v = b_lambert_w0<B>(z.v);
   if constexpr (P > 0) {
     const B inv = t_rcp(b_exp(r.v) * (B(1) + r.v));
-#pragma unroll
-    for (int i = 0; i < P; ++i) r.d[i] = z.d[i] * inv;
+    r.d.scale(z.d, inv);
   }
   return r;
 }

@@ -284,7 +284,7 @@ template <class T, class A> HGF_D void pe_continuous(const A& a, T* s, int node)
   const T delta = HGF_S(node, F_MEAN) - HGF_S(node, F_EXPECTED_MEAN);
   const T pi_hat = HGF_S(node, F_EXPECTED_PRECISION);
   HGF_S(node, F_VALUE_PREDICTION_ERROR) = delta;
-  T vope = pi_hat / HGF_S(node, F_PRECISION) + pi_hat * (delta * delta) - B(1);
+  T vope = pi_hat / HGF_S(node, F_PRECISION) + pi_hat * x_square(delta) - B(1);
   if (a.n_volp(node) > 0) vope = vope / static_cast<B>(a.n_volp(node));
   HGF_S(node, F_VOLATILITY_PREDICTION_ERROR) = vope;
 }
@@ -453,7 +453,7 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   using B = base_t<T>;
   const T prev_var = x_max(c.prev_variance, static_cast<B>(1e-128));
   const T delta = c.mean - c.expected_mean;
-  const T be = B(1) / c.precision + delta * delta;  // E[(x - mu_hat)^2] under the child's posterior
+  const T be = B(1) / c.precision + x_square(delta);  // E[(x - mu_hat)^2] under the child's posterior
   const B log_dt = st.log_dt;
   const T log_prev_var = x_log(prev_var);
   T gamma;
@@ -485,7 +485,7 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   }
   const T log_den = x_logaddexp(log_prev_var, log_s2);
   const T w2 = x_sigmoid(log_s2 - log_prev_var);
-  const T da2 = be * x_exp(-log_den) - B(1);
+  const T da2 = be * x_exp_neg(log_den) - B(1);
   T pi2_full, pi2_alt;
   if constexpr (EXPLICIT) {
     const auto k2 = kappa * kappa;
@@ -510,15 +510,15 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   else { arg1 = log_dt + mu1; arg2 = log_dt + mu2; }
   const T l1 = x_logaddexp(log_prev_var, arg1);
   const T e1 = mu1 - mu_hat;
-  const T i1 = B(-0.5) * l1 - B(0.5) * be * x_exp(-l1) - B(0.5) * pi_hat * (e1 * e1);
+  const T i1 = B(-0.5) * l1 - B(0.5) * be * x_exp_neg(l1) - B(0.5) * pi_hat * x_square(e1);
   const T l2 = x_logaddexp(log_prev_var, arg2);
   const T e2 = mu2 - mu_hat;
-  const T i2 = B(-0.5) * l2 - B(0.5) * be * x_exp(-l2) - B(0.5) * pi_hat * (e2 * e2);
+  const T i2 = B(-0.5) * l2 - B(0.5) * be * x_exp_neg(l2) - B(0.5) * pi_hat * x_square(e2);
   const T b = x_sigmoid(i2 - i1);
   // moment-matched mixture
   post_mean = (B(1) - b) * mu1 + b * mu2;
   const T dm = mu1 - mu2;
-  post_precision = B(1) / ((B(1) - b) / pi1 + b / pi2 + b * (B(1) - b) * (dm * dm));
+  post_precision = B(1) / ((B(1) - b) / pi1 + b / pi2 + b * (B(1) - b) * x_square(dm));
 }
 
 // continuous_node_posterior_update_unbounded.py:13-48; reads only the first
@@ -591,7 +591,7 @@ template <class T, class A> HGF_D void pe_volatile(const A& a, T* s, const Step<
   using B = base_t<T>;
   const T delta = HGF_S(node, F_MEAN) - HGF_S(node, F_EXPECTED_MEAN);
   const T pi_hat = HGF_S(node, F_EXPECTED_PRECISION);
-  const T vope = pi_hat / HGF_S(node, F_PRECISION) + pi_hat * (delta * delta) - B(1);
+  const T vope = pi_hat / HGF_S(node, F_PRECISION) + pi_hat * x_square(delta) - B(1);
   HGF_S(node, F_VALUE_PREDICTION_ERROR) = delta;
   HGF_S(node, F_VOLATILITY_PREDICTION_ERROR) = vope;
   const B cap = static_cast<B>(a.max_posterior_precision());
@@ -680,8 +680,7 @@ template <class TR, class T> HGF_D TR widen(const T& x) {
     return x;
   } else {
     TR r(pv(x));
-#pragma unroll
-    for (int i = 0; i < scalar_traits<T>::n_tangents; ++i) r.d[i] = x.d[i];
+    r.d.widen_from(x.d, scalar_traits<T>::n_tangents);
     return r;
   }
 }

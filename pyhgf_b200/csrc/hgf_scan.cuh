@@ -107,7 +107,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
     if constexpr (PF > 0) {
 #pragma unroll
       for (int i = 0; i < PF; ++i)
-        if (i == q - args.tangent_offset) v.d[i] = B(1);
+        if (i == q - args.tangent_offset) v.d.set(i, B(1));
     }
     const int slot = lists.param_slot[q];
     if constexpr (Topo::is_static) {
@@ -125,7 +125,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
   for (int q = lists.n_filter; q < lists.n_params; ++q) {
     TR v = TR(HGF_LDG(params + static_cast<long long>(lists.param_row[q]) * N + n));
     if constexpr (PR > 0) {
-      if (q == args.resp_index) v.d[PF] = B(1);
+      if (q == args.resp_index) v.d.set(PF, B(1));
     }
     const int j = lists.param_slot[q] - a.slot_resp();
 #pragma unroll
@@ -271,10 +271,10 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
 #pragma unroll
         for (int i = 0; i < PF; ++i)
           if (args.tangent_offset + i < lists.n_filter)
-            grad[static_cast<long long>(lists.param_row[args.tangent_offset + i]) * N + n] = scale * total.d[i];
+            grad[static_cast<long long>(lists.param_row[args.tangent_offset + i]) * N + n] = scale * total.d.get(i);
       }
       if constexpr (PR > 0) {
-        if (args.resp_index >= 0) grad[static_cast<long long>(lists.param_row[args.resp_index]) * N + n] = scale * total.d[PF];
+        if (args.resp_index >= 0) grad[static_cast<long long>(lists.param_row[args.resp_index]) * N + n] = scale * total.d.get(PF);
       }
     }
     // the final attribute vector is an interpreter-only output (hgf_static_run.h routes such calls there):
