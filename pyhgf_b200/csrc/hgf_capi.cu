@@ -43,8 +43,8 @@ int report_error(const char* msg) { return fail("%s", msg); }
 }  // namespace hgf
 
 // gradient_mode auto: the reverse sweep is taken when forward mode would need this many passes (4 filter parameters + 1
-// response parameter each).  Measured: the sweep costs 3.4-3.6 plain filters whatever P is, one
-// forward-mode pass 1.4-2.5, two passes 3.6-6.6.
+// response parameter each).  Measured: the sweep costs 3.6-3.9 plain filters whatever P is, one
+// forward-mode pass 1.4-2.4, two passes 3.4-5.4.
 constexpr int kReverseFromPasses = 2;
 
 struct hgf_plan {

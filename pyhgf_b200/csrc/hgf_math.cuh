@@ -78,7 +78,7 @@ HGF_HD double b_fma(double a, double b, double c) { return ::fma(a, b, c); }
 // multiplier as a broadcast operand.  Lane throughput is that of two scalar instructions (tools/ubench/pipes.cu), but it
 // is ONE issue slot, and the logp+grad kernels are issue-bound: the 3-level binary HGF with two filter tangents executes
 // 797 warp-instructions per instance-step unpacked, most of them tangent arithmetic on the FP32 pipe.  Same IEEE
-// operations in the same order as the generic form (an odd P pads the last pair with a lane that is never read).
+// operations in the same order as the generic form (an odd P keeps its last tangent as a scalar).
 #ifndef HGF_PACKED_TANGENTS
 #define HGF_PACKED_TANGENTS 1
 #endif
@@ -186,56 +186,72 @@ template <class B, int P> struct Tan<B, P, false> {
   }
 };
 template <int P> struct Tan<float, P, true> {
-  static constexpr int NP = (P + 1) / 2;
+  static constexpr int NP = P / 2;        // whole pairs
+  static constexpr bool ODD = (P & 1) != 0;  // an odd P keeps its last tangent as a scalar (a padded pair would spend a lane)
   F2 e[NP];
-  HGF_HD float get(int i) const { return (i & 1) ? f2_hi(e[i >> 1]) : f2_lo(e[i >> 1]); }
+  float last;
+  HGF_HD float get(int i) const {
+    if (ODD && i == P - 1) return last;
+    return (i & 1) ? f2_hi(e[i >> 1]) : f2_lo(e[i >> 1]);
+  }
   HGF_HD void set(int i, float x) {
+    if (ODD && i == P - 1) { last = x; return; }
     F2& p = e[i >> 1];
     p = (i & 1) ? f2_make(f2_lo(p), x) : f2_make(x, f2_hi(p));
   }
   HGF_HD void zero() {
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k].u = 0ull;
+    last = 0.0f;
   }
   HGF_HD void add(const Tan& a, const Tan& b) {
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k] = f2_add(a.e[k], b.e[k]);
+    if constexpr (ODD) last = a.last + b.last;
   }
   HGF_HD void sub(const Tan& a, const Tan& b) {
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k] = f2_sub(a.e[k], b.e[k]);
+    if constexpr (ODD) last = a.last - b.last;
   }
   HGF_HD void neg(const Tan& a) {  // (a * -1: an exact sign flip, zeros included)
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k] = f2_scale(a.e[k], -1.0f);
+    if constexpr (ODD) last = -a.last;
   }
   HGF_HD void scale(const Tan& a, float s) {
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k] = f2_scale(a.e[k], s);
+    if constexpr (ODD) last = a.last * s;
   }
   HGF_HD void product(const Tan& a, float bv, float av, const Tan& b) {
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k] = f2_fma(a.e[k], bv, f2_scale(b.e[k], av));
+    if constexpr (ODD) last = b_fma(a.last, bv, av * b.last);
   }
   HGF_HD void quotient(float q, const Tan& b, const Tan& a, float inv) {
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k] = f2_scale(f2_fma(b.e[k], -q, a.e[k]), inv);
+    if constexpr (ODD) last = b_fma(-q, b.last, a.last) * inv;
   }
   HGF_HD void blend(const Tan& a, float wa, const Tan& b, float wb) {
 #pragma unroll
     for (int k = 0; k < NP; ++k) e[k] = f2_fma(a.e[k], wa, f2_scale(b.e[k], wb));
+    if constexpr (ODD) last = b_fma(a.last, wa, b.last * wb);
   }
-  template <class T2> HGF_HD void widen_from(const T2& a, int n) {
+  template <class T2> HGF_HD void widen_from(const T2& a, int n) {  // the first n tangents of a (the others keep their value)
 #pragma unroll
     for (int i = 0; i < P; ++i)
       if (i < n) set(i, a.get(i));
   }
   template <int P2> HGF_HD void widen_from(const Tan<float, P2, true>& a, int n) {  // whole pairs move as pairs
-    constexpr int NP2 = (P2 + 1) / 2;
+    constexpr int NP2 = P2 / 2;
 #pragma unroll
     for (int k = 0; k < NP; ++k)
       if (k < NP2 && 2 * k + 1 < n) e[k] = a.e[k];
-      else if (k < NP2 && 2 * k < n) e[k] = f2_make(f2_lo(a.e[k]), f2_hi(e[k]));
+#pragma unroll
+    for (int i = 0; i < P; ++i)
+      if (i < n && i < P2 && !((i >> 1) < NP && (i >> 1) < NP2 && 2 * (i >> 1) + 1 < n)) set(i, a.get(i));
   }
 };
 

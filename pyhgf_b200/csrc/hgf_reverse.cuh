@@ -9,7 +9,7 @@
 //      undo the operations one by one: restore the slots, recompute that ONE operation's intermediates in registers and
 //      run its adjoint statements.  The adjoint attribute vector `sb` carries lambda_t to step t-1 through the carried
 //      slots and accumulates d logp / d attribute in every slot no operation writes (the parameters).
-// Cost: 3.4-3.6 plain filters measured (profiles/r2_grad_scaling.log), whatever the number of parameters; the attribute
+// Cost: 3.6-3.9 plain filters measured (profiles/r2_grad_scaling.log), whatever the number of parameters; the attribute
 // vector, its adjoint and the undo log of one step live in registers (every index is a literal after inlining).
 #pragma once
 #ifdef __CUDACC__

@@ -17,7 +17,7 @@ Here the adjoint of ONE time step is written out ahead of time, as straight-line
     clip`` follow the selected branch.
 
 csrc/hgf_reverse.cuh holds the kernel around it: a forward sweep that stores the carried beliefs of every step (the
-checkpoints: 2 floats per continuous node), then the backward sweep over time.  Measured, the sweep costs 3.4-3.6 plain
+checkpoints: 2 floats per continuous node), then the backward sweep over time.  Measured, the sweep costs 3.6-3.9 plain
 filters whatever the number of parameters; the forward-mode kernels (hgf_math.cuh, Dual<>) cost 1.4-2.5 plain filters per
 pass of up to 4 filter parameters + 1 response parameter, so the library takes the sweep as soon as forward mode would
 need a second pass (profiles/r2_grad_scaling.log).
