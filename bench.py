@@ -627,8 +627,10 @@ def run_gpu(args):
             "roofline": roofline, **extra,
             "e2e": {"value": w_e2e.units_per_eval * R / e2e_step_s, "unit": "node-updates/s", "instances_per_gpu": w_e2e.n_local, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": 1e3 * e2e_step_s, "steps": e2e_steps,
-                    "api": ("hgf_logp_grad_host" if w.gradient else "hgf_filter_host") + " (C ABI, pinned host buffers; on several GPUs the per-chain sums it "
-                           "returns are the all-reduced ones)", "matches_device_path": same},
+                    "api": ("hgf_logp_grad_host" if w.gradient else "hgf_filter_host") + " (C ABI, pinned host buffers" +
+                           ("; the per-chain sums it returns are the ALL-REDUCED ones: every call includes the exchange)" if fused is not None
+                            else "; no cross-GPU exchange in this leg: the HGF_BENCH_COLLECTIVE=nccl arm reduces on the device path only)" if world > 1 and w.n_chains
+                            else ")"), "matches_device_path": same},
             "gpu_launches": int(launches),
             "clocks": ck,
         }
