@@ -96,14 +96,14 @@ HGF_HD F2 f2_make(float lo, float hi) {
 }
 HGF_HD float f2_lo(F2 x) {
 #ifdef __CUDA_ARCH__
-  float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x.u)); return lo;
+  float lo; asm("mov.b64 {%0, _}, %1;" : "=f"(lo) : "l"(x.u)); return lo;
 #else
   const unsigned int a = static_cast<unsigned int>(x.u); float f; __builtin_memcpy(&f, &a, 4); return f;
 #endif
 }
 HGF_HD float f2_hi(F2 x) {
 #ifdef __CUDA_ARCH__
-  float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x.u)); return hi;
+  float hi; asm("mov.b64 {_, %0}, %1;" : "=f"(hi) : "l"(x.u)); return hi;
 #else
   const unsigned int a = static_cast<unsigned int>(x.u >> 32); float f; __builtin_memcpy(&f, &a, 4); return f;
 #endif
