@@ -148,8 +148,9 @@ typedef struct {
    * like lax.switch).  Device pointer for hgf_filter / hgf_logp_grad, host pointer for the *_host entry points. */
   const int32_t* branch_idx;
   /* hgf_logp_grad only: how the gradient is computed.  0 (auto): forward-mode tangents carried in the filter's registers
-   * (up to 4 filter parameters + 1 response parameter per pass); when that would take two or more passes and the topology has a
-   * generated one, the checkpointed REVERSE sweep (forward over time storing the carried beliefs, then backward with
+   * (up to 4 filter parameters + 1 response parameter per pass); when that would take two or more passes -- or the plan's
+   * kernels include no register-resident gradient kernel at all -- and the topology has a generated one, the checkpointed
+   * REVERSE sweep (forward over time storing the carried beliefs, then backward with
    * the adjoint of every update: cost independent of the number of parameters).  1: forward-mode always.  2: the reverse
    * sweep (error if the plan's topology has none, or the call asks for trajectories / pointwise output / a fused
    * cross-GPU reduction, which only the forward-mode kernels produce). */

@@ -359,7 +359,10 @@ static int launch(const hgf_plan_t* plan, const hgf_call_t* c, cudaStream_t stre
                                                                           : "this plan's topology has no generated reverse sweep");
     const int n_resp = lists.n_params - lists.n_filter;
     const int forward_passes = std::max((lists.n_filter + 3) / 4, n_resp);
-    if (available && (c->gradient_mode == 2 || forward_passes >= kReverseFromPasses)) {
+    // no register-resident gradient kernel in this variant (e.g. the 16-node network): forward mode would be the interpreter's
+    const unsigned mask = c->dtype == 32 ? plan->variant->mask32 : plan->variant->mask64;
+    const bool native_forward = (mask & ~1u) != 0;
+    if (available && (c->gradient_mode == 2 || forward_passes >= kReverseFromPasses || !native_forward)) {
       lists.n_filter = lists.n_params;
       const cudaError_t rerr = plan->variant->reverse(plan->prog, lists, a, c->dtype, stream, &n_launched);
       g_launches += n_launched;

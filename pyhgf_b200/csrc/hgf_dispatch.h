@@ -21,6 +21,10 @@ struct KernelVariant {
   bool (*matches)(const Program&);  // nullptr: accepts every program
   RunFn run;
   ReverseFn reverse = nullptr;
+  // the register-resident kernels this variant was built with, per scalar type (variant_bit in hgf_launch_decl.h; 0 for the
+  // interpreter, which runs everything): a gradient call whose variant has no gradient kernel of its own would fall to the
+  // interpreter's forward mode, so the launcher prefers the generated reverse sweep there whatever the parameter count
+  unsigned mask32 = 0, mask64 = 0;
 };
 
 // hgf_interp.cu

@@ -16,7 +16,7 @@ static constexpr ReverseFn kSpecialisedReverse = HGF_REV_FN;
 static constexpr ReverseFn kSpecialisedReverse = nullptr;
 #endif
 static const KernelVariant kSpecialised = {HGF_TOPO_LABEL, topo_matches<HGF_TOPO_TYPE>, run_static_any<HGF_TOPO_TYPE, HGF_MASK32, HGF_MASK64>,
-                                           kSpecialisedReverse};
+                                           kSpecialisedReverse, HGF_MASK32, HGF_MASK64};
 }
 
 extern "C" const void* hgf_specialisation_variant() { return &hgf::kSpecialised; }

@@ -25,7 +25,7 @@ template <int> struct no_reverse { static constexpr ReverseFn fn = nullptr; };
 
 #define HGF_STATIC_TOPO(name, mask32, mask64, rev)                                                   \
   static const KernelVariant kVariant_##name = {"static:" #name, topo_matches<Topo_##name>,          \
-                                                run_static_any<Topo_##name, mask32, mask64>, rev};
+                                                run_static_any<Topo_##name, mask32, mask64>, rev, mask32, mask64};
 #if __has_include(<generated/static_table.inc>)
 #include <generated/static_table.inc>
 #endif

@@ -479,6 +479,15 @@ def test_reverse_sweep_16_node_network(G, R):
             for i, k in enumerate(keys[sl]):
                 got = res.gradient[k].cpu().numpy()
                 assert np.allclose(got, want_g[i], rtol=1e-7, atol=1e-7 * max(np.abs(want_g[i]).max(), 1e-300)), (rname, k)
+        # a FEW parameters: forward mode would be one pass, but this topology has no register-resident gradient kernel (it would
+        # be the interpreter's): gradient=True takes the sweep, bit for bit the explicit "reverse" result
+        few = dict(zip(keys[:3], vals[:3]))
+        a = net.batch(x, few, response_function=rfn, gradient=True)
+        b = net.batch(x, few, response_function=rfn, gradient="reverse")
+        f = net.batch(x, few, response_function=rfn, gradient="forward")
+        for k in few:
+            assert np.array_equal(a.gradient[k].cpu().numpy(), b.gradient[k].cpu().numpy()), k
+            assert np.allclose(a.gradient[k].cpu().numpy(), f.gradient[k].cpu().numpy(), rtol=1e-7, atol=1e-7 * float(f.gradient[k].abs().max())), k
         r32 = nets.ghgf16(G.Network, dtype="float32").batch(x, dict(zip(keys, vals)), response_function=rfn, gradient="reverse")
         s64 = res.surprise.cpu().numpy()
         assert np.median(np.abs(r32.surprise.double().cpu().numpy() - s64) / np.abs(s64)) < 1e-5
