@@ -468,6 +468,52 @@ template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, const
   dual_div_primal(a.v, b.v, r.v, P > 0, [&](B inv) { r.d.quotient(r.v, b.d, a.d, inv); });
   return r;
 }
+// A denominator together with its MUFU.RCP seed, so that SEVERAL quotients by the same value -- or by twice it -- cost ONE SFU
+// operation: a / x and c / x, and a / (2 x) through rcp(2 x) = rcp(x) / 2 (the approximation acts on the mantissa: a power of
+// two changes the exponent only, so the shared seed gives the bits a seed of its own would: tools/ubench/rcp_scaling.cu finds
+// 0 mismatches over every mantissa, sign and exponent with |x| < 2^125, profiles/r2_rcp_scaling.log; beyond, rcp(2 x) is
+// subnormal and flushed -- the denominators here are precisions capped at max_posterior_precision = 1e10).  Under the IEEE policies (HGF_DIV_MODE 2, the validation build, double, the host build without
+// SFU emulation) the seed is unused and `a / recip` is the true division a / x: nothing changes there.
+#if defined(HGF_SFU_TANGENTS) && HGF_DIV_MODE != 2
+#define HGF_SHARED_RCP 1
+#else
+#define HGF_SHARED_RCP 0
+#endif
+template <class T> struct Recip {
+  T x;
+  base_t<T> r0;
+};
+template <class B, int P> HGF_HD Recip<Dual<B, P>> x_recip(const Dual<B, P>& x) {
+  Recip<Dual<B, P>> r;
+  r.x = x;
+  r.r0 = B(0);
+#if HGF_SHARED_RCP
+  if constexpr (sizeof(B) == 4) r.r0 = sfu_rcp(x.v);
+#endif
+  return r;
+}
+template <class B, int P> HGF_HD Recip<Dual<B, P>> recip_twice(const Recip<Dual<B, P>>& a) {  // of 2 x
+  Recip<Dual<B, P>> r;
+  r.x = B(2) * a.x;
+  r.r0 = B(0.5) * a.r0;
+  return r;
+}
+template <class T> HGF_HD Recip<T> x_where(bool c, const Recip<T>& a, const Recip<T>& b) { return c ? a : b; }
+template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, const Recip<Dual<B, P>>& b) {
+#if HGF_SHARED_RCP
+  if constexpr (sizeof(B) == 4) {
+    Dual<B, P> r;
+    r.v = div_from_rcp(a.v, b.x.v, b.r0);
+    if constexpr (P > 0) r.d.quotient(r.v, b.x.d, a.d, b.r0);
+    return r;
+  } else {
+    return a / b.x;
+  }
+#else
+  return a / b.x;
+#endif
+}
+
 // a / b with the primal quotient at IEEE accuracy under every policy (see exact_div_from_rcp)
 template <int P> HGF_HD Dual<float, P> exact_div(const Dual<float, P>& a, const Dual<float, P>& b) {
   Dual<float, P> r;

@@ -461,14 +461,18 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   // expansion 1: around the prediction
   const T w1 = x_sigmoid(gamma - log_prev_var);
   const T da1 = c.expected_precision * be - B(1);
+  // (quotients by pi1, 2 pi1 and by pi2 share one reciprocal per denominator: hgf_math.cuh::Recip -- same bits, fewer SFU ops)
   T pi1, mu1, pi_y;
+  Recip<T> over_pi1;
   if constexpr (EXPLICIT) {
     pi1 = pi_hat + B(0.5) * (kappa * kappa) * w1 * (B(1) - w1);
-    mu1 = mu_hat + (kappa * w1 / (B(2) * pi1)) * da1;
+    over_pi1 = x_recip(pi1);
+    mu1 = mu_hat + (kappa * w1 / recip_twice(over_pi1)) * da1;
     pi_y = pi_hat / (kappa * kappa);
   } else {
     pi1 = pi_hat + B(0.5) * w1 * (B(1) - w1);
-    mu1 = mu_hat + (w1 / (B(2) * pi1)) * da1;
+    over_pi1 = x_recip(pi1);
+    mu1 = mu_hat + (w1 / recip_twice(over_pi1)) * da1;
     pi_y = pi_hat;
   }
   // expansion 2: around the Lambert-W mode
@@ -496,13 +500,14 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
     pi2_alt = pi_hat + B(0.5) * w2 * (B(1) - w2);
   }
   const T pi2_safe = x_where(pv(pi2_full) <= B(0), pi2_alt, pi2_full);
+  const Recip<T> over_pi2_safe = x_recip(pi2_safe);
   T mu2_safe;
-  if constexpr (EXPLICIT) mu2_safe = x_star + (B(0.5) * kappa * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe;
-  else mu2_safe = x_star + (B(0.5) * w2 * da2 - pi_hat * (x_star - mu_hat)) / pi2_safe;
+  if constexpr (EXPLICIT) mu2_safe = x_star + (B(0.5) * kappa * w2 * da2 - pi_hat * (x_star - mu_hat)) / over_pi2_safe;
+  else mu2_safe = x_star + (B(0.5) * w2 * da2 - pi_hat * (x_star - mu_hat)) / over_pi2_safe;
   // fall back to expansion 1 wherever expansion 2 is not finite ("double where",
   // continuous_node_posterior_update_unbounded.py:173-177)
   const bool ok = x_isfinite(pi2_safe) && x_isfinite(mu2_safe);
-  const T pi2 = x_where(ok, pi2_safe, pi1);
+  const Recip<T> over_pi2 = x_where(ok, over_pi2_safe, over_pi1);  // pi2 = where(ok, pi2_safe, pi1), with its reciprocal
   const T mu2 = x_where(ok, mu2_safe, mu1);
   // variational energies at both candidate means
   T arg1, arg2;
@@ -518,7 +523,7 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   // moment-matched mixture
   post_mean = (B(1) - b) * mu1 + b * mu2;
   const T dm = mu1 - mu2;
-  post_precision = B(1) / ((B(1) - b) / pi1 + b / pi2 + b * (B(1) - b) * x_square(dm));
+  post_precision = B(1) / ((B(1) - b) / over_pi1 + b / over_pi2 + b * (B(1) - b) * x_square(dm));
 }
 
 // continuous_node_posterior_update_unbounded.py:13-48; reads only the first
