@@ -473,8 +473,10 @@ template <class B, int P> HGF_HD Dual<B, P> operator/(const Dual<B, P>& a, const
 // two changes the exponent only, so the shared seed gives the bits a seed of its own would: tools/ubench/rcp_scaling.cu finds
 // 0 mismatches over every mantissa, sign and exponent with |x| < 2^125, profiles/r2_rcp_scaling.log; beyond, rcp(2 x) is
 // subnormal and flushed -- the denominators here are precisions capped at max_posterior_precision = 1e10).  Under the IEEE policies (HGF_DIV_MODE 2, the validation build, double, the host build without
-// SFU emulation) the seed is unused and `a / recip` is the true division a / x: nothing changes there.
-#if defined(HGF_SFU_TANGENTS) && HGF_DIV_MODE != 2
+// SFU emulation) the seed is unused and `a / recip` is the true division a / x: nothing changes there.  (What the KERNELS
+// return with and without the sharing -- identical gradient kernels, a plain filter that rounds one product elsewhere:
+// tools/shared_rcp_check.py.)
+#if defined(HGF_SFU_TANGENTS) && HGF_DIV_MODE != 2 && !defined(HGF_NO_SHARED_RCP)  // (-DHGF_NO_SHARED_RCP: the test's twin)
 #define HGF_SHARED_RCP 1
 #else
 #define HGF_SHARED_RCP 0

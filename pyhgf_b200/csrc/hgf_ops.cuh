@@ -461,7 +461,7 @@ HGF_D void unbounded_mixture(const Step<T>& st, const VolatilityChild<T>& c, con
   // expansion 1: around the prediction
   const T w1 = x_sigmoid(gamma - log_prev_var);
   const T da1 = c.expected_precision * be - B(1);
-  // (quotients by pi1, 2 pi1 and by pi2 share one reciprocal per denominator: hgf_math.cuh::Recip -- same bits, fewer SFU ops)
+  // (quotients by pi1, 2 pi1 and by pi2 share one reciprocal per denominator: hgf_math.cuh::Recip -- the same seeds, fewer SFU ops)
   T pi1, mu1, pi_y;
   Recip<T> over_pi1;
   if constexpr (EXPLICIT) {

@@ -8,6 +8,8 @@ float64 launches are held to 1e-9.  Everything here needs a B200: run with ``-m 
 """
 
 import ctypes as C
+import json
+import os
 
 import numpy as np
 import pytest
@@ -956,6 +958,24 @@ def test_on_demand_specialisation_with_reverse_sweep(G, R, scheme):
     for i, k in enumerate(keys):
         assert np.allclose(res.gradient[k].cpu().numpy()[ok], want_g[i][ok], rtol=1e-7, atol=1e-7 * np.abs(want_g[i][ok]).max()), k
     assert revgen.Unsupported is not None  # (node kinds outside the scan -- ef-state, categorical -- raise it; none is built here)
+
+
+def test_shared_reciprocals_against_a_build_without_them():
+    """hgf_math.cuh::Recip -- one MUFU.RCP per denominator of the unbounded update serving a / x, c / x and a / (2 x) -- against
+    a build of the same kernels WITHOUT it (-DHGF_NO_SHARED_RCP): the gradient kernels return the same bits, logp and
+    gradients; the plain filter differs by the placement of one rounding (nvcc fuses the other product of a two-product
+    sum) and stays within 1e-5 on 99 % of the instances; two builds with the same flags are identical
+    (tools/shared_rcp_check.py, in its own process: a registered specialisation would serve every later plan of the
+    topology in this one; tools/ubench/rcp_scaling.cu is the primitive's own check)."""
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "shared_rcp_check.py")], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert not any(line["control_same_flags_differing"].values()), line
+    assert not any(v for w, v in line["values_differing_in_any_bit"].items() if w != "filter logp"), line
 
 
 def test_generative_rollouts(G, datasets):
