@@ -412,13 +412,20 @@ template <class B> __global__ void fused_wait_kernel(void* workspace, int G, int
 #ifndef HGF_WIDE_MIN_BLOCKS
 #define HGF_WIDE_MIN_BLOCKS 1  // resident 64-thread blocks per SM asked of the wide (> 8 nodes) float32 specialisations
 #endif
+#ifndef HGF_MID_MIN_BLOCKS
+#define HGF_MID_MIN_BLOCKS 8  // the same for 5 .. 8 nodes (tools/bench_c5_blocks.py measures 7 and 6 against it)
+#endif
 template <class T, class Topo> constexpr int scan_min_blocks() {
   if constexpr (!Topo::is_static) return 1; else
-  return sizeof(base_t<T>) != 4 ? 1 : (Topo::kNodes <= 4 ? 7 : (Topo::kNodes <= 8 ? 8 : HGF_WIDE_MIN_BLOCKS));
+  return sizeof(base_t<T>) != 4 ? 1 : (Topo::kNodes <= 4 ? 7 : (Topo::kNodes <= 8 ? HGF_MID_MIN_BLOCKS : HGF_WIDE_MIN_BLOCKS));
 }
 
 template <class T, class Topo, int NSLOTS, int PR, bool UNIT_DT, bool REC>
+#ifdef HGF_SCAN_MAXNREG  // experiments only (tools/bench_c5_blocks.py): an explicit register cap instead of a residency bound
+__global__ void __maxnreg__(HGF_SCAN_MAXNREG)
+#else
 __global__ void __launch_bounds__(SCAN_THREADS, scan_min_blocks<T, Topo>())
+#endif
 scan_kernel(const __grid_constant__ Program prog, const __grid_constant__ CallLists lists, const __grid_constant__ ScanArgs args) {
   using B = base_t<T>;
   long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
