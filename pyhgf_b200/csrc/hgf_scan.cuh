@@ -150,6 +150,34 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
 
   TR total = TR(B(0));
   bool node1_mean_nan = false;
+  // the static leaf set in slot order: f(leaf number, value)
+  auto for_each_leaf = [&](auto&& f) {
+    int leaf = 0;
+#pragma unroll
+    for (int node = 0; node < a.n_nodes(); ++node) {
+#pragma unroll
+      for (int fld = 0; fld < 4; ++fld, ++leaf) f(leaf, pv(HGF_S(node, fld)));
+      if (a.node_type(node) == NODE_VOLATILE) {
+#pragma unroll
+        for (int fld = F_MEAN_VOL; fld < F_MEAN_VOL + 4; ++fld, ++leaf) f(leaf, pv(HGF_S(node, fld)));
+      }
+    }
+  };
+  // EVERY leaf recorded (config 5): row = leaf number, so the step's stores need no mask test, no branch and no computed offset
+  bool rec_all = false;
+  (void)for_each_leaf;
+  if constexpr (REC && Topo::is_static) {
+    int n_leaves = 0;
+#pragma unroll
+    for (int node = 0; node < a.n_nodes(); ++node) n_leaves += a.node_type(node) == NODE_VOLATILE ? 8 : 4;
+    rec_all = true;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const int bits = n_leaves - 32 * w;
+      const uint32_t full = bits >= 32 ? 0xffffffffu : (bits <= 0 ? 0u : (1u << bits) - 1u);
+      rec_all = rec_all && args.rec_mask[w] == full;
+    }
+  }
 
   for (int t = 0; t < T_steps; ++t) {
     Step<T> st;
@@ -222,23 +250,17 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
       const long long leaf_stride = static_cast<long long>(T_steps) * N;
       if constexpr (Topo::is_static) {
         // static leaf set (see ScanArgs::rec_mask): warp-uniform predicates
-        int leaf = 0, row = 0;
-#pragma unroll
-        for (int node = 0; node < a.n_nodes(); ++node) {
-#pragma unroll
-          for (int f = 0; f < 4; ++f, ++leaf)
+        if (rec_all) {
+          if (col) for_each_leaf([&](int leaf, B v) { col[leaf * SCAN_THREADS] = v; });
+          else for_each_leaf([&](int leaf, B v) { direct[leaf * leaf_stride] = v; });
+        } else {
+          int row = 0;
+          for_each_leaf([&](int leaf, B v) {
             if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) {
-              if (col) col[row * SCAN_THREADS] = pv(HGF_S(node, f)); else direct[row * leaf_stride] = pv(HGF_S(node, f));
+              if (col) col[row * SCAN_THREADS] = v; else direct[row * leaf_stride] = v;
               ++row;
             }
-          if (a.node_type(node) == NODE_VOLATILE) {
-#pragma unroll
-            for (int f = F_MEAN_VOL; f < F_MEAN_VOL + 4; ++f, ++leaf)
-              if (args.rec_mask[leaf >> 5] >> (leaf & 31) & 1u) {
-                if (col) col[row * SCAN_THREADS] = pv(HGF_S(node, f)); else direct[row * leaf_stride] = pv(HGF_S(node, f));
-                ++row;
-              }
-          }
+          });
         }
       } else {
         for (int r = 0; r < lists.n_rec; ++r) {
