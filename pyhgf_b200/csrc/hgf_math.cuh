@@ -766,8 +766,8 @@ template <class B> HGF_D B b_logaddexp(B a, B b) {
   B amax = (a >= b || b_isnan(a)) ? a : b;
   if (b_isnan(b)) amax = b;
   const B delta = a - b;
-  if (b_isnan(delta)) return a + b;
-  return amax + b_log1p(b_exp(-b_abs(delta)));
+  const B r = amax + b_log1p(b_exp(-b_abs(delta)));
+  return b_isnan(delta) ? a + b : r;  // (a select, not an early return: no branch in the step's straight-line code)
 }
 HGF_D float x_logaddexp(float a, float b) { return b_logaddexp<float>(a, b); }
 HGF_D double x_logaddexp(double a, double b) { return b_logaddexp<double>(a, b); }
