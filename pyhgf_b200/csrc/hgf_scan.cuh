@@ -170,7 +170,7 @@ HGF_D response_scalar_t<T, PR> scan_instance(const Program& prog, const CallList
     int n_leaves = 0;
 #pragma unroll
     for (int node = 0; node < a.n_nodes(); ++node) n_leaves += a.node_type(node) == NODE_VOLATILE ? 8 : 4;
-    rec_all = true;
+    rec_all = n_leaves <= 128;  // (the mask holds 128 leaves: a larger topology with its first 128 recorded is NOT "all")
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
       const int bits = n_leaves - 32 * w;
