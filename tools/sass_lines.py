@@ -1,6 +1,7 @@
 """Per-source-line instruction histogram of a kernel's time loop, from `nvdisasm --print-line-info` (needs -lineinfo).
     cuobjdump -xelf all obj.o; nvdisasm --print-line-info X.cubin | python tools/sass_lines.py <function-substring> [top]
-The loop is the longest backward branch of the function (as in tools/sass_loop.py)."""
+The loop is the longest backward branch of the function that contains MUFU instructions (as in tools/sass_loop.py);
+tools/sass_branches.py does the same for the branches only, following the inlining chain."""
 import collections, re, sys
 flt, top = sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 40
 lines = sys.stdin.read().splitlines()
@@ -32,7 +33,9 @@ for a, t, _ in body:
     m = re.search(r"BRA\S*\s+.*\.L_x_(\d+)", t)
     if m and m.group(1) in labels:
         tgt = labels[m.group(1)]
-        if tgt < a and (best is None or a - tgt > best[1] - best[0]):
+        # the time loop is the longest backward branch whose body holds SFU work (an unrolled attribute-load loop
+        # ahead of it can be longer in a large topology)
+        if tgt < a and (best is None or a - tgt > best[1] - best[0]) and any(tgt <= a2 <= a and "MUFU" in t2 for a2, t2, _ in body):
             best = (tgt, a)
 lo, hi = best
 per_line, per_op = collections.Counter(), collections.defaultdict(collections.Counter)
